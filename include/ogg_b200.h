@@ -1,0 +1,132 @@
+/*
+ * ogg_b200.h -- C ABI of libogg_b200.so: the B200 (sm_100a) supergrid hot path of
+ * ocean_model_grid_generator.
+ *
+ * Each entry point stands where one Python function of the reference stands
+ * (ocean_grid_generator.py, cited as OGG:first-last).  Conventions:
+ *   - every `double*` / `const double*` is a DEVICE pointer owned by the caller, row-major, j (latitude
+ *     row) outer, i (longitude) inner; the library never frees caller memory;
+ *   - sizes are int64_t, reals are double (FP64 throughout, FMA contraction disabled in the kernels);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are asynchronous
+ *     with respect to the host unless stated; scratch memory is stream-ordered (cudaMallocAsync);
+ *   - return value: 0 on success, OGG_ERR_* below, or OGG_ERR_CUDA - (int)cudaError_t.  Nothing throws.
+ * There is no CPU fallback: without a CUDA device every compute entry point returns an error.
+ */
+#ifndef OGG_B200_H_
+#define OGG_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OGG_OK 0
+#define OGG_ERR_UNCODED_ORDER (-1)   /* reference: Exception("Uncoded order")      OGG:204,222,255 */
+#define OGG_ERR_ORDER_NOT_CODED (-2) /* reference: Exception("order not coded")    OGG:547,562     */
+#define OGG_ERR_SHAPE (-3)           /* reference: shape-mismatch exceptions        OGG:229,722     */
+#define OGG_ERR_ARG (-4)
+#define OGG_ERR_CUDA (-1000)
+
+/* flags of ogg_band_fill_metrics */
+#define OGG_BAND_SKIP_TOP_VERTEX_ROW 1 /* do not write row nyp-1 of x, y, dx, angle_dx (the "[:-1]" of OGG:1316-1362) */
+#define OGG_BAND_NO_METRICS 2          /* --skip_metrics: dx, dy, area are left untouched                               */
+
+const char* ogg_version(void);
+/* number of CUDA devices visible (0 when there is no GPU; never fails) */
+int ogg_device_count(void);
+
+/* ---- portable elementary functions, element-wise (numpypi.numpypi_series stand-ins; OGG:5) ------------- */
+int ogg_sin(const double* in, double* out, int64_t n, void* stream);
+int ogg_cos(const double* in, double* out, int64_t n, void* stream);
+int ogg_tan(const double* in, double* out, int64_t n, void* stream);
+int ogg_arcsin(const double* in, double* out, int64_t n, void* stream);
+int ogg_arccos(const double* in, double* out, int64_t n, void* stream);
+int ogg_arctan(const double* in, double* out, int64_t n, void* stream);
+int ogg_exp(const double* in, double* out, int64_t n, void* stream);
+int ogg_log(const double* in, double* out, int64_t n, void* stream);
+int ogg_sinh(const double* in, double* out, int64_t n, void* stream);
+int ogg_cosh(const double* in, double* out, int64_t n, void* stream);
+int ogg_mod360(const double* in, double* out, int64_t n, void* stream); /* numpy.mod(x, 360.0), OGG:684 */
+int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* stream);
+
+/* ---- spherical bands (Mercator / Southern Ocean / regular cap) ------------------------------------------ */
+/* Fused tile + MIDAS metrics + angle for a band whose mesh is the outer product of lam[nxp] and phi[nyp]:
+ * replaces np.tile (OGG:430-432, 840-841) + generate_grid_metrics_MIDAS (OGG:687-716, latlon_areafix=True)
+ * + angle_x (OGG:719-729).  Outputs (any may be NULL): x, y, angle [nyp][nxp]; dx [nyp][nxp-1];
+ * dy [nyp-1][nxp]; area [nyp-1][nxp-1]. */
+int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int64_t nxp, double Re, int flags,
+                          double* x, double* y, double* dx, double* dy, double* area, double* angle, void* stream);
+/* generate_grid_metrics_MIDAS (OGG:687-716) on a supplied mesh.  halo_x/halo_y (both or neither; [nxp]) are
+ * the mesh row that follows row nyp-1 on the next row-slab; when given, dy and area get nyp rows instead of
+ * nyp-1. */
+int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp, double Re, int latlon_areafix,
+                      const double* halo_x, const double* halo_y, double* dx, double* dy, double* area,
+                      void* stream);
+/* angle_x (OGG:719-729) */
+int ogg_angle_x(const double* x, const double* y, int64_t nyp, int64_t nxp, double* angle, void* stream);
+
+/* ---- bipolar (Murray tripolar) Arctic cap ----------------------------------------------------------------- */
+/* bipolar_projection (OGG:33-100), element-wise on n points.  metrics_only!=0: lams, phis may be NULL. */
+int ogg_bipolar_projection(const double* lamg, const double* phig, int64_t n, double lon_bp, double rp,
+                           int metrics_only, double* lams, double* phis, double* h_i_inv, double* h_j_inv,
+                           void* stream);
+/* generate_bipolar_cap_mesh (OGG:103-122), mesh rows [j0, j1) of the (Nj+1) x (Ni+1) cap (row drop for
+ * ensure_nj_even is the caller's).  lams, phis [j1-j0][Ni+1]; h_i_inv [j1-j0][Ni] and
+ * h_j_inv [min(j1,Nj)-j0][Ni+1] may be NULL. */
+int ogg_bipolar_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lat0_bp, double lon_bp, double rp,
+                         double* lams, double* phis, double* h_i_inv, double* h_j_inv, void* stream);
+/* bipolar_cap_ij_array (OGG:125-133): fractional index vectors i[ni], j[nj] -> h_i_inv, h_j_inv [nj][ni] */
+int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64_t nj, int64_t Ni, int64_t Nj_ncap,
+                             double lat0_bp, double lon_bp, double rp, double* h_i_inv, double* h_j_inv,
+                             void* stream);
+/* bipolar_cap_metrics_quad_fast (OGG:136-188) for cell rows [j0, j1) of an nx x ny cap.
+ * dxq [(j1-j0) + (j1==ny)][nx]  (the extra row is the pole row dxq[ny,:]);  dyq [j1-j0][nx+1];  daq [j1-j0][nx]. */
+int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lat0_bp,
+                                 double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
+                                 void* stream);
+
+/* ---- quadrature helpers (OGG:191-255), batched --------------------------------------------------------------- */
+/* a[n], b[n] are HOST pointers */
+int ogg_quad_positions(int n, double* a_host, double* b_host);
+/* quad_average on m vectors y[m][n] -> out[m] */
+int ogg_quad_average(const double* y, int64_t m, int n, double* out, void* stream);
+/* quad_average_2d on m squares y[m][n][n] -> out[m] */
+int ogg_quad_average_2d(const double* y, int64_t m, int n, double* out, void* stream);
+
+/* ---- displaced-pole southern cap ---------------------------------------------------------------------------------- */
+/* r_joint and z_0 of OGG:494-495 -> out3 = {r_joint, Re z_0, Im z_0} (device) */
+int ogg_dp_constants(double lat0, double lam_pole, double r_pole, double* out3, void* stream);
+/* displacedPoleCap_projection (OGG:447-467) incl. monotonic_bounding with x_0 = lon_grid[0,0] */
+int ogg_dp_projection(const double* lon_grid, const double* lat_grid, int64_t nj, int64_t ni, double z0_re,
+                      double z0_im, double r_joint, double* lam, double* phi, void* stream);
+/* monotonic_bounding (OGG:470-475), in place on x[nj][ni] */
+int ogg_monotonic_bounding(double* x, int64_t nj, int64_t ni, double x_0, void* stream);
+/* displacedPoleCap_mesh (OGG:478-506, excluded_fraction=None) on index vectors i[nil], j[njl] */
+int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int64_t ni, int64_t nj, double lon0,
+                double lat0, double lam_pole, double r_pole, double* lams, double* phis, void* stream);
+/* great_arc_distance (OGG:522-532) -> out[njl][nil] */
+int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl,
+                           int64_t nil, int64_t nx, int64_t ny, double lon0, double lat0, double lon_dp,
+                           double r_dp, double* out, void* stream);
+/* numerical_hi (direction=0, OGG:535-547) / numerical_hj (direction=1, OGG:550-562) -> out[njl][nil] */
+int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i, int64_t nil, int64_t nx, int64_t ny,
+                    double lon0, double lat0, double lon_dp, double r_dp, double eps, int order, double* out,
+                    void* stream);
+/* displacedPoleCap_metrics_quad (OGG:565-601) for cell rows [j0, j1); output shapes as the bipolar twin */
+int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lon0, double lat0,
+                        double lon_dp, double r_dp, double Re, double* dxq, double* dyq, double* daq, void* stream);
+
+/* ---- reductions for metrics_error (OGG:747-756) and the global-area check ------------------------------------------- */
+/* out[0] = sum_{k<n} a[k*stride]   (fixed-shape tree: deterministic for given n) */
+int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, void* stream);
+
+/* ---- measurement aid: FP64 add/mul issue rate (no FMA), the cap kernels' roofline denominator ------------------------ */
+/* runs iters dependent DADD/DMUL pairs x 8 independent chains per thread on every SM; returns via *gops_host the
+ * achieved 1e9 instructions/s.  Synchronous. */
+int ogg_fp64_issue_rate(int64_t iters, double* ginstr_per_s_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OGG_B200_H_ */

@@ -1,0 +1,110 @@
+"""ctypes binding of libogg_b200.so (C ABI declared in include/ogg_b200.h).
+
+No CPU fallback lives here or anywhere in the package: a missing library, a missing symbol or a
+missing GPU raises immediately.
+"""
+import ctypes
+import os
+
+from . import build as _build
+
+_LIB = None
+_dp = ctypes.c_void_p
+_i64 = ctypes.c_int64
+_d = ctypes.c_double
+_int = ctypes.c_int
+_vp = ctypes.c_void_p
+
+OGG_BAND_SKIP_TOP_VERTEX_ROW = 1
+OGG_BAND_NO_METRICS = 2
+
+# name -> argtypes, exactly as declared in include/ogg_b200.h
+SIGNATURES = {
+    "ogg_sin": [_dp, _dp, _i64, _vp], "ogg_cos": [_dp, _dp, _i64, _vp], "ogg_tan": [_dp, _dp, _i64, _vp],
+    "ogg_arcsin": [_dp, _dp, _i64, _vp], "ogg_arccos": [_dp, _dp, _i64, _vp], "ogg_arctan": [_dp, _dp, _i64, _vp],
+    "ogg_exp": [_dp, _dp, _i64, _vp], "ogg_log": [_dp, _dp, _i64, _vp], "ogg_sinh": [_dp, _dp, _i64, _vp],
+    "ogg_cosh": [_dp, _dp, _i64, _vp], "ogg_mod360": [_dp, _dp, _i64, _vp],
+    "ogg_arctan2": [_dp, _dp, _dp, _i64, _vp],
+    "ogg_band_fill_metrics": [_dp, _dp, _i64, _i64, _d, _int, _dp, _dp, _dp, _dp, _dp, _dp, _vp],
+    "ogg_metrics_midas": [_dp, _dp, _i64, _i64, _d, _int, _dp, _dp, _dp, _dp, _dp, _vp],
+    "ogg_angle_x": [_dp, _dp, _i64, _i64, _dp, _vp],
+    "ogg_bipolar_projection": [_dp, _dp, _i64, _d, _d, _int, _dp, _dp, _dp, _dp, _vp],
+    "ogg_bipolar_cap_mesh": [_i64, _i64, _i64, _i64, _d, _d, _d, _dp, _dp, _dp, _dp, _vp],
+    "ogg_bipolar_cap_ij_array": [_dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _dp, _dp, _vp],
+    "ogg_bipolar_cap_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _dp, _vp],
+    "ogg_quad_positions": [_int, ctypes.POINTER(_d), ctypes.POINTER(_d)],
+    "ogg_quad_average": [_dp, _i64, _int, _dp, _vp],
+    "ogg_quad_average_2d": [_dp, _i64, _int, _dp, _vp],
+    "ogg_dp_constants": [_d, _d, _d, _dp, _vp],
+    "ogg_dp_projection": [_dp, _dp, _i64, _i64, _d, _d, _d, _dp, _dp, _vp],
+    "ogg_monotonic_bounding": [_dp, _i64, _i64, _d, _vp],
+    "ogg_dp_mesh": [_dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
+    "ogg_great_arc_distance": [_dp, _dp, _dp, _dp, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _vp],
+    "ogg_numerical_h": [_int, _dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _vp],
+    "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _dp, _dp, _dp, _vp],
+    "ogg_sum_strided": [_dp, _i64, _i64, _dp, _vp],
+    "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
+    "ogg_device_count": [],
+    "ogg_version": [],
+}
+
+OGG_ERR_UNCODED_ORDER = -1
+OGG_ERR_ORDER_NOT_CODED = -2
+OGG_ERR_SHAPE = -3
+OGG_ERR_ARG = -4
+OGG_ERR_CUDA = -1000
+
+
+class OggError(RuntimeError):
+    pass
+
+
+def library_path():
+    return _build.LIB
+
+
+def load(build_if_missing=True):
+    """dlopen the library and set every prototype; raises if it cannot be had."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        if not build_if_missing:
+            raise OggError("libogg_b200.so is missing (%s); run __graft_entry__.build()" % path)
+        _build.build()
+    lib = ctypes.CDLL(path)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.argtypes = argtypes
+        fn.restype = ctypes.c_char_p if name == "ogg_version" else _int
+    _LIB = lib
+    return lib
+
+
+def check(rc, what=""):
+    """Map a status to the reference's exception vocabulary (SURVEY 8(b) error conventions)."""
+    if rc == 0:
+        return
+    if rc == OGG_ERR_UNCODED_ORDER:
+        raise Exception("Uncoded order")
+    if rc == OGG_ERR_ORDER_NOT_CODED:
+        raise Exception("order not coded")
+    if rc == OGG_ERR_SHAPE:
+        raise Exception("Input arrays do not have the same shape!")
+    if rc == OGG_ERR_ARG:
+        raise OggError("invalid argument to %s" % what)
+    if rc <= OGG_ERR_CUDA:
+        raise OggError("CUDA error %d in %s" % (OGG_ERR_CUDA - rc, what))
+    raise OggError("status %d from %s" % (rc, what))
+
+
+def call(name, *args):
+    lib = load()
+    check(getattr(lib, name)(*args), name)
+
+
+def require_gpu():
+    lib = load()
+    if lib.ogg_device_count() < 1:
+        raise OggError("no CUDA device: this package has no CPU path (see oracle/ for the test-only CPU oracle)")

@@ -1,0 +1,1354 @@
+// ogg_b200.cu -- sm_100a kernels + C ABI (include/ogg_b200.h) for the supergrid hot path.
+//
+// Compile with -fmad=false: the reference's arithmetic is numpy element-wise math, one rounding per
+// operation, and bit parity with it (and with the CPU oracle) depends on never contracting a*b+c.
+// "OGG:n" = /root/reference/ocean_grid_generator.py line n.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+
+#include "../../include/ogg_b200.h"
+#include "ogg_trig.cuh"
+
+namespace ogg {
+
+using i64 = long long;
+
+// ------------------------------------------------------------------------------------------------
+// host helpers
+// ------------------------------------------------------------------------------------------------
+#define OGG_CUDA(call)                                        \
+  do {                                                        \
+    cudaError_t e__ = (call);                                 \
+    if (e__ != cudaSuccess) return OGG_ERR_CUDA - (int)e__;   \
+  } while (0)
+#define OGG_LAUNCH_CHECK() OGG_CUDA(cudaGetLastError())
+
+static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+static inline unsigned cdiv_u(i64 a, i64 b) { return static_cast<unsigned>((a + b - 1) / b); }
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+// stream-ordered scratch
+struct Scratch {
+  cudaStream_t st;
+  void* ptrs[16];
+  int n = 0;
+  explicit Scratch(cudaStream_t s) : st(s) {}
+  template <typename T>
+  cudaError_t get(T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) + 16, st);
+    if (e != cudaSuccess) return e;
+    ptrs[n++] = q;
+    *p = static_cast<T*>(q);
+    return cudaSuccess;
+  }
+  ~Scratch() {
+    for (int k = 0; k < n; ++k) cudaFreeAsync(ptrs[k], st);
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// element-wise portable functions
+// ------------------------------------------------------------------------------------------------
+enum Fn { F_SIN, F_COS, F_TAN, F_ASIN, F_ACOS, F_ATAN, F_EXP, F_LOG, F_SINH, F_COSH, F_MOD360 };
+
+template <int F>
+OGG_DI double apply_fn(double x) {
+  if (F == F_SIN) return p_sin(x);
+  if (F == F_COS) return p_cos(x);
+  if (F == F_TAN) return p_tan(x);
+  if (F == F_ASIN) return p_asin(x);
+  if (F == F_ACOS) return p_acos(x);
+  if (F == F_ATAN) return p_atan(x);
+  if (F == F_EXP) return p_exp(x);
+  if (F == F_LOG) return p_log(x);
+  if (F == F_SINH) return p_sinh(x);
+  if (F == F_COSH) return p_cosh(x);
+  return mod360(x);
+}
+
+template <int F>
+__global__ void __launch_bounds__(256) k_unary(const double* __restrict__ in, double* __restrict__ out, i64 n) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x)
+    out[e] = apply_fn<F>(in[e]);
+}
+__global__ void __launch_bounds__(256) k_atan2(const double* __restrict__ y, const double* __restrict__ x,
+                                               double* __restrict__ out, i64 n) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x)
+    out[e] = p_atan2(y[e], x[e]);
+}
+
+static unsigned flat_grid(i64 n, int per_sm = 8) {
+  i64 want = (n + 255) / 256;
+  i64 cap = (i64)num_sms() * per_sm;
+  return static_cast<unsigned>(want < 1 ? 1 : (want < cap ? want : cap));
+}
+
+template <int F>
+static int launch_unary(const double* in, double* out, i64 n, void* stream) {
+  if (n < 0 || (n > 0 && (!in || !out))) return OGG_ERR_ARG;
+  if (n == 0) return OGG_OK;
+  k_unary<F><<<flat_grid(n), 256, 0, S(stream)>>>(in, out, n);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// spherical bands: fused tile + MIDAS + angle  (x = lam[i], y = phi[j])
+// ------------------------------------------------------------------------------------------------
+// column table: dxi[i] (OGG:696), hx[i] = 0.5*(dxi+dxi) (OGG:713), xd[i] = x[ia]-x[ib] (OGG:725-727)
+// row table:    cl[j] = cos(lv) (OGG:695,698), cy[j] = cos(y*PI_180) (OGG:725), dyr[j] (OGG:699-702),
+//               dsl[j] = sl[j+1]-sl[j] (OGG:711,713)
+__global__ void __launch_bounds__(256) k_band_tables(const double* __restrict__ lam, const double* __restrict__ phi,
+                                                     i64 nyp, i64 nxp, double Re, double* __restrict__ dxi,
+                                                     double* __restrict__ hx, double* __restrict__ xd,
+                                                     double* __restrict__ cl, double* __restrict__ cy,
+                                                     double* __restrict__ dyr, double* __restrict__ dsl) {
+  const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (t < nxp) {
+    const i64 i = t;
+    if (i < nxp - 1) {
+      const double d = mdist(lam[i + 1], lam[i]) * kPi180;
+      dxi[i] = d;
+      hx[i] = 0.5 * (d + d);
+    }
+    const i64 ia = i == nxp - 1 ? i : i + 1, ib = i == 0 ? i : i - 1;
+    xd[i] = lam[ia] - lam[ib];
+  }
+  if (t < nyp) {
+    const i64 j = t;
+    const double yj = phi[j];
+    const double lv = (0.5 * (yj + yj)) * kPi180;
+    const SinCos q = sincos_parts(lv);
+    cl[j] = cos_of(q);
+    cy[j] = p_cos(yj * kPi180);
+    if (j < nyp - 1) {
+      const double yu = phi[j + 1];
+      const double lu = (0.5 * (yu + yj)) * kPi180;
+      const double dx_j = mdist(lam[0], lam[0]) * kPi180;  // same-column longitudes: exactly what OGG:700 sees
+      const double dy_j = (yu - yj) * kPi180;
+      const double tt = dx_j * p_cos(lu);
+      dyr[j] = Re * sqrt(dy_j * dy_j + tt * tt);
+      const double lvu = (0.5 * (yu + yu)) * kPi180;
+      dsl[j] = p_sin(lvu) - sin_of(q);
+    }
+  }
+}
+
+constexpr int kBandRows = 8;
+__global__ void __launch_bounds__(256) k_band_fill(const double* __restrict__ lam, const double* __restrict__ phi,
+                                                   const double* __restrict__ dxi, const double* __restrict__ hx,
+                                                   const double* __restrict__ xd, const double* __restrict__ cl,
+                                                   const double* __restrict__ cy, const double* __restrict__ dyr,
+                                                   const double* __restrict__ dsl, i64 nyp, i64 nxp, i64 nyp_v,
+                                                   double Re, double Re2, int metrics, double* __restrict__ x,
+                                                   double* __restrict__ y, double* __restrict__ dx,
+                                                   double* __restrict__ dy, double* __restrict__ area,
+                                                   double* __restrict__ angle) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i >= nxp) return;
+  const i64 nx = nxp - 1;
+  const bool cell = i < nx;
+  const double lamv = lam[i], xdv = xd[i];
+  const double dxiv = cell ? dxi[i] : 0.0, hxv = cell ? hx[i] : 0.0;
+  const i64 jb = (i64)blockIdx.y * kBandRows;
+#pragma unroll
+  for (int r = 0; r < kBandRows; ++r) {
+    const i64 j = jb + r;
+    if (j >= nyp) break;
+    const double phij = phi[j];
+    if (j < nyp_v) {
+      if (x) x[j * nxp + i] = lamv;
+      if (y) y[j * nxp + i] = phij;
+      if (angle) {
+        const double dyc = phij - phij;  // y[ia]-y[ib] on a band
+        angle[j * nxp + i] = p_atan2(dyc, xdv * cy[j]) / kPi180;
+      }
+      if (metrics && cell && dx) {
+        const double dy_i = (phij - phij) * kPi180;
+        const double tt = dxiv * cl[j];
+        dx[j * nx + i] = Re * sqrt(dy_i * dy_i + tt * tt);
+      }
+    }
+    if (metrics && j < nyp - 1) {
+      if (dy) dy[j * nxp + i] = dyr[j];
+      if (cell && area) area[j * nx + i] = Re2 * (hxv * dsl[j]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// general MIDAS metrics on a supplied mesh (OGG:687-716)
+// ------------------------------------------------------------------------------------------------
+// One thread per column, a strip of kMidasRows mesh rows per block row; the j/j+1 stencil is carried in
+// registers down the strip (row j of one step = row j-1 of the next), the i+1 neighbour comes from the next
+// lane by warp shuffle (lane 31 reads it from memory).
+constexpr int kMidasRows = 32;
+__global__ void __launch_bounds__(128) k_midas(const double* __restrict__ x, const double* __restrict__ y, i64 nyp,
+                                               i64 nxp, double Re, double Re2, int areafix,
+                                               const double* __restrict__ halo_x, const double* __restrict__ halo_y,
+                                               double* __restrict__ dx, double* __restrict__ dy,
+                                               double* __restrict__ area) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  const i64 nx = nxp - 1;
+  const i64 nrows = nyp + (halo_x ? 1 : 0);  // mesh rows available incl. halo
+  const i64 jb = (i64)blockIdx.y * kMidasRows;
+  const bool in = i < nxp, cell = i < nx;
+  const unsigned lane = threadIdx.x & 31u;
+  double xp = 0, yp = 0, dxip = 0, slp = 0;  // previous row
+  for (int r = 0; r <= kMidasRows; ++r) {
+    const i64 j = jb + r;
+    if (j >= nrows) break;
+    const double* xr = j < nyp ? x + j * nxp : halo_x;
+    const double* yr = j < nyp ? y + j * nxp : halo_y;
+    const double xc = in ? xr[i] : 0.0, yc = in ? yr[i] : 0.0;
+    double xn = __shfl_down_sync(0xffffffffu, xc, 1);
+    double yn = __shfl_down_sync(0xffffffffu, yc, 1);
+    if (lane == 31u && cell) { xn = xr[i + 1]; yn = yr[i + 1]; }
+    double dxi = 0, sl = 0;
+    if (cell) {
+      const double lv = (0.5 * (yn + yc)) * kPi180;       // :695
+      dxi = mdist(xn, xc) * kPi180;                       // :696
+      const double dyi = (yn - yc) * kPi180;              // :697
+      const SinCos q = sincos_parts(lv);
+      const double tt = dxi * cos_of(q);
+      if (r < kMidasRows && j < nyp && dx) dx[j * nx + i] = Re * sqrt(dyi * dyi + tt * tt);  // :698
+      sl = sin_of(q);                                     // :711
+    }
+    if (r > 0 && in) {
+      const i64 jm = j - 1;
+      if (dy) {
+        const double lu = (0.5 * (yc + yp)) * kPi180;     // :699
+        const double dxj = mdist(xc, xp) * kPi180;        // :700
+        const double dyj = (yc - yp) * kPi180;            // :701
+        const double tt = dxj * p_cos(lu);
+        dy[jm * nxp + i] = Re * sqrt(dyj * dyj + tt * tt);  // :702
+      }
+      if (cell && area && areafix) area[jm * nx + i] = Re2 * ((0.5 * (dxi + dxip)) * (sl - slp));  // :713
+    }
+    xp = xc; yp = yc; dxip = dxi; slp = sl;
+  }
+}
+// latlon_areafix=False branch (OGG:715); dx has nyp_a+1 rows available (halo-aware callers pass the extra row)
+__global__ void __launch_bounds__(256) k_area_nofix(const double* __restrict__ dx, const double* __restrict__ dxtop,
+                                                    const double* __restrict__ dy, i64 ny, i64 nx,
+                                                    double* __restrict__ area) {
+  const i64 n = ny * nx;
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    const i64 j = e / nx, i = e - j * nx;
+    const double up = (dxtop && j == ny - 1) ? dxtop[i] : dx[(j + 1) * nx + i];
+    area[e] = 0.25 * ((up + dx[j * nx + i]) * (dy[j * (nx + 1) + i + 1] + dy[j * (nx + 1) + i]));
+  }
+}
+// dx of a single (halo) row: used only by the areafix=False + halo combination
+__global__ void __launch_bounds__(256) k_dx_row(const double* __restrict__ xr, const double* __restrict__ yr, i64 nx,
+                                                double Re, double* __restrict__ out) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i >= nx) return;
+  const double lv = (0.5 * (yr[i + 1] + yr[i])) * kPi180;
+  const double dxi = mdist(xr[i + 1], xr[i]) * kPi180;
+  const double dyi = (yr[i + 1] - yr[i]) * kPi180;
+  const double tt = dxi * p_cos(lv);
+  out[i] = Re * sqrt(dyi * dyi + tt * tt);
+}
+
+// angle_x (OGG:719-729)
+__global__ void __launch_bounds__(256) k_angle(const double* __restrict__ x, const double* __restrict__ y, i64 nyp,
+                                               i64 nxp, double* __restrict__ angle) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i >= nxp) return;
+  const i64 ia = i == nxp - 1 ? i : i + 1, ib = i == 0 ? i : i - 1;
+  for (i64 j = blockIdx.y; j < nyp; j += gridDim.y) {
+    const double* xr = x + j * nxp;
+    const double* yr = y + j * nxp;
+    const double a = p_atan2(yr[ia] - yr[ib], (xr[ia] - xr[ib]) * p_cos(yr[i] * kPi180));
+    angle[j * nxp + i] = a / kPi180;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// bipolar cap (OGG:33-133)
+// ------------------------------------------------------------------------------------------------
+struct BpRow { double sphig, beta2_inv, N_inv; };   // depends on the latitude index only
+struct BpCol { double sinla, alpha2, dl; };         // depends on the longitude index only
+
+OGG_DI BpRow bp_row(double phig_in, double rp) {
+  const double phig = 90 - ((2 * p_atan(p_tan((0.5 * (90 - phig_in)) * kPi180) / rp)) / kPi180);  // :41
+  const SinCos q = sincos_parts(phig * kPi180);
+  BpRow o;
+  o.sphig = sin_of(q);                                   // :44
+  const double tb = tan_of(q);
+  o.beta2_inv = tb * tb;                                 // :46
+  const double chig = (90 - phig) * kPi180;              // :75
+  const double tg = p_tan(chig / 2);
+  const double qg = rp * tg;
+  const double rden2 = 1.0 / (1 + qg * qg);              // :76
+  const double N = (rp * (1 + tg * tg)) * rden2;         // :77
+  o.N_inv = 1 / N;                                       // :78
+  return o;
+}
+OGG_DI BpCol bp_col(double lamg, double lon_bp) {
+  const double tmp = mdist(lamg, lon_bp) * kPi180;       // :42
+  const SinCos q = sincos_parts(tmp);
+  BpCol o;
+  o.sinla = sin_of(q);                                   // :43
+  const double ca = cos_of(q);
+  o.alpha2 = ca * ca;                                    // :45
+  o.dl = lamg - lon_bp;
+  return o;
+}
+template <bool FULL>
+OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, double& lams, double& phis,
+                      double& h_i_inv, double& h_j_inv) {
+  const double alpha2 = C.alpha2, beta2_inv = R.beta2_inv;
+  const double rden = 1.0 / (1.0 + alpha2 * beta2_inv);  // :47
+  const bool huge = fabs(beta2_inv) > kHuge;
+  if (FULL) {
+    double B = C.sinla * sqrt(rden);                     // :50
+    if (huge) B = 0.0;                                   // :52
+    double lamc = p_asin(B) / kPi180;                    // :53
+    const double dl = C.dl;
+    if (dl > 90 && dl <= 180) lamc = 180 - lamc;         // :58
+    if (dl > 180 && dl <= 270) lamc = 180 + lamc;        // :59
+    if (dl > 270) lamc = 360 - lamc;                     // :60
+    if (dl == 90) lamc = 90;                             // :62
+    if (dl == 270) lamc = 270;                           // :63
+    lams = lamc + lon_bp;                                // :64
+  }
+  const double A = C.sinla * R.sphig;                    // :68
+  const double chic = p_acos(A);                         // :69
+  const double tc = p_tan(chic / 2);
+  const double q = rp * tc;
+  phis = 90 - ((2 * p_atan(q)) / kPi180);                // :70
+  const double rden2 = 1.0 / (1 + q * q);                // :72
+  const double M_inv = (rp * (1 + tc * tc)) * rden2;     // :73
+  const double cp = p_cos(phis * kPi180);
+  const double cos2phis = cp * cp;                       // :79
+  const double MM = M_inv * M_inv, r2 = rden * rden;
+  double hj = ((((cos2phis * alpha2) * (1 - alpha2)) * beta2_inv) * (1 + beta2_inv)) * r2 +
+              (MM * (1 - alpha2)) * rden;                // :81-84
+  if (huge) hj = MM;                                     // :86
+  h_j_inv = sqrt(hj) * R.N_inv;                          // :87
+  double hi = (cos2phis * (1 + beta2_inv)) * r2 + ((MM * alpha2) * beta2_inv) * rden;  // :89-92
+  if (huge) hi = MM;                                     // :94
+  h_i_inv = sqrt(hi);                                    // :95
+}
+
+__global__ void __launch_bounds__(256) k_bp_projection(const double* __restrict__ lamg, const double* __restrict__ phig,
+                                                       i64 n, double lon_bp, double rp, int metrics_only,
+                                                       double* __restrict__ lams, double* __restrict__ phis,
+                                                       double* __restrict__ hi, double* __restrict__ hj) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    const BpRow R = bp_row(phig[e], rp);
+    const BpCol C = bp_col(lamg[e], lon_bp);
+    double l = 0, p, a, b;
+    if (metrics_only) bp_sample<false>(R, C, lon_bp, rp, l, p, a, b);
+    else bp_sample<true>(R, C, lon_bp, rp, l, p, a, b);
+    if (!metrics_only) { lams[e] = l; phis[e] = p; }
+    if (hi) hi[e] = a;
+    if (hj) hj[e] = b;
+  }
+}
+
+// index -> coordinate tables.  iv/jv NULL: integer indices i0+t / j0+t (generate_bipolar_cap_mesh :113,:115);
+// otherwise fractional indices (bipolar_cap_ij_array :126-127).
+__global__ void __launch_bounds__(256) k_bp_tables(const double* __restrict__ iv, i64 i0, i64 ncol,
+                                                   const double* __restrict__ jv, i64 j0, i64 nrow, i64 Ni, i64 Nj,
+                                                   double lat0_bp, double lon_bp, double rp, BpCol* __restrict__ ct,
+                                                   BpRow* __restrict__ rt) {
+  const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (t < ncol) {
+    const double idx = iv ? iv[t] : (double)(i0 + t);
+    ct[t] = bp_col(lon_bp + (idx * 360.0) / (double)Ni, lon_bp);
+  }
+  if (t < nrow) {
+    const double idx = jv ? jv[t] : (double)(j0 + t);
+    rt[t] = bp_row(lat0_bp + (idx * (90 - lat0_bp)) / (double)Nj, rp);
+  }
+}
+
+// MODE 0: mesh (:118-120): lams, phis + optionally scaled h's with the mesh's trimming
+// MODE 1: metrics-only samples (:130-132): scaled h_i_inv, h_j_inv on the full lattice
+template <int MODE>
+__global__ void __launch_bounds__(256) k_bp_lattice(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt,
+                                                    i64 nrow, i64 ncol, i64 Ni, i64 Nj, i64 jrow0, double lat0_bp,
+                                                    double lon_bp, double rp, double* __restrict__ o0,
+                                                    double* __restrict__ o1, double* __restrict__ o2,
+                                                    double* __restrict__ o3) {
+  const i64 c = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  const BpCol C = ct[c];
+  for (i64 r = blockIdx.y; r < nrow; r += gridDim.y) {
+    const BpRow R = rt[r];
+    double l = 0, p, a, b;
+    if (MODE == 0) {
+      bp_sample<true>(R, C, lon_bp, rp, l, p, a, b);
+      o0[r * ncol + c] = l;
+      o1[r * ncol + c] = p;
+      if (o2 && c < ncol - 1) o2[r * (ncol - 1) + c] = ((a * 2) * kPi) / (double)Ni;                        // :119
+      if (o3 && jrow0 + r < Nj) o3[r * ncol + c] = ((b * kPi180) * (90 - lat0_bp)) / (double)Nj;            // :120
+    } else {
+      bp_sample<false>(R, C, lon_bp, rp, l, p, a, b);
+      o0[r * ncol + c] = ((a * 2) * kPi) / (double)Ni;                                                      // :131
+      o1[r * ncol + c] = ((b * (90 - lat0_bp)) * kPi180) / (double)Nj;                                      // :132
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Gauss-Lobatto quadrature (OGG:191-255) on a lattice of UNIQUE samples
+// ------------------------------------------------------------------------------------------------
+struct QuadNodes { double a[5], b[5]; };
+
+static int quad_nodes_host(int n, QuadNodes* q) {  // :191-204 (plain IEEE ops, no trig)
+  if (n == 2) { q->a[0] = 0.0; q->a[1] = 1.0; q->b[0] = 1.0; q->b[1] = 0.0; return 0; }
+  if (n == 3) { q->a[0] = 0.0; q->a[1] = 0.5; q->a[2] = 1.0; q->b[0] = 1.0; q->b[1] = 0.5; q->b[2] = 0.0; return 0; }
+  if (n == 4) {
+    const double r5 = 0.5 / std::sqrt(5.0);
+    q->a[0] = 0.0; q->a[1] = 0.5 - r5; q->a[2] = 0.5 + r5; q->a[3] = 1.0;
+    q->b[0] = 1.0; q->b[1] = 0.5 + r5; q->b[2] = 0.5 - r5; q->b[3] = 0.0;
+    return 0;
+  }
+  if (n == 5) {
+    const double r37 = 0.5 * std::sqrt(3.0 / 7.0);
+    q->a[0] = 0.0; q->a[1] = 0.5 - r37; q->a[2] = 0.5; q->a[3] = 0.5 + r37; q->a[4] = 1.0;
+    q->b[0] = 1.0; q->b[1] = 0.5 + r37; q->b[2] = 0.5; q->b[3] = 0.5 - r37; q->b[4] = 0.0;
+    return 0;
+  }
+  return -1;
+}
+
+// Unique sample indices for cells [c0, c1): position u = (n-1)*(c-c0)+k holds b[k]*c + a[k]*(c+1)  (:145,:155),
+// k < n-1; the closing entry u = (n-1)*(c1-c0) is cell c1-1's last node b[n-1]*(c1-1) + a[n-1]*c1.
+// fudge: if that closing value equals `total` it becomes total-0.001 (:146-147) and one more entry
+// holding cell `total`'s first node (the exact pole row used by dxq[ny,:]) is appended.
+__global__ void __launch_bounds__(256) k_sample_index(QuadNodes q, int n, i64 c0, i64 c1, i64 total, int fudge,
+                                                      double* __restrict__ out) {
+  const i64 nu = (n - 1) * (c1 - c0) + 1;
+  const i64 u = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (u < nu) {
+    i64 c = c0 + u / (n - 1);
+    int k = (int)(u % (n - 1));
+    if (u == nu - 1) { c = c1 - 1; k = n - 1; }
+    double v = q.b[k] * (double)c + q.a[k] * (double)(c + 1);
+    if (fudge && u == nu - 1 && v == (double)total) v = (double)total - 0.001;
+    out[u] = v;
+  }
+  if (fudge && c1 == total && u == nu) out[u] = q.b[0] * (double)total + q.a[0] * (double)(total + 1);
+}
+
+template <int N>
+OGG_DI double quad_avg_1d(const double* y) {  // :207-222
+  if constexpr (N == 2) return (1.0 / 2.0) * (y[0] + y[1]);
+  else if constexpr (N == 3) return (1.0 / 6.0) * (4.0 * y[1] + (y[0] + y[2]));
+  else if constexpr (N == 4) return (1.0 / 12.0) * (5.0 * (y[1] + y[2]) + (y[0] + y[3]));
+  else return (1.0 / 180.0) * ((64.0 * y[2] + (49.0 * (y[1] + y[3]))) + 9.0 * (y[0] + y[4]));
+}
+template <int N>
+OGG_DI double quad_avg_2d(const double (&y)[N][N]) {  // :225-255
+  if constexpr (N == 2) {
+    const double d = 1.0 / 2.0;
+    return (d * d) * (((y[0][0] + y[0][1]) + y[1][0]) + y[1][1]);
+  } else if constexpr (N == 3) {
+    const double d = 1.0 / 6.0;
+    const double inner = (((y[0][1] + y[1][0]) + y[1][2]) + y[2][1]) + 4.0 * y[1][1];
+    const double outer = (((y[0][0] + y[0][2]) + y[2][0]) + y[2][2]) + 4.0 * inner;
+    return (d * d) * outer;
+  } else {
+    constexpr double w4[5] = {1.0, 5.0, 5.0, 1.0, 0.0};
+    constexpr double w5[5] = {9.0, 49.0, 64.0, 49.0, 9.0};
+    const double d = N == 4 ? 1.0 / 12.0 : 1.0 / 180.0;
+    double ysum = 0.0;
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+#pragma unroll
+      for (int i = 0; i < N; ++i) ysum = ysum + ((N == 4 ? w4[i] : w5[i]) * (N == 4 ? w4[j] : w5[j])) * y[j][i];
+    return (d * d) * ysum;
+  }
+}
+
+// Cell sums (OGG:180-187 / :591-599) for cell rows [0, ncr) of a chunk whose unique sample rows start at the
+// chunk's first cell.  sx, sy: [nur][nuc] unique samples (dx, dy).  top_row >= 0: unique row feeding the extra
+// dxq row (pole row) written at dxq row ncr.
+template <int N>
+__global__ void __launch_bounds__(128) k_quad_cells(const double* __restrict__ sx, const double* __restrict__ sy,
+                                                    i64 nuc, i64 ncr, i64 nx, i64 top_row, double Re,
+                                                    double* __restrict__ dxq, double* __restrict__ dyq,
+                                                    double* __restrict__ daq) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i > nx) return;
+  for (i64 j = blockIdx.y; j <= ncr; j += gridDim.y) {
+    const i64 c0 = (N - 1) * i;
+    if (j == ncr) {
+      if (top_row >= 0 && i < nx) dxq[j * nx + i] = quad_avg_1d<N>(sx + top_row * nuc + c0) * Re;  // :183,:186
+      continue;
+    }
+    const i64 r0 = (N - 1) * j;
+    if (i < nx) {
+      double prod[N][N];
+#pragma unroll
+      for (int jj = 0; jj < N; ++jj)
+#pragma unroll
+        for (int ii = 0; ii < N; ++ii) {
+          const i64 o = (r0 + jj) * nuc + c0 + ii;
+          prod[jj][ii] = sx[o] * sy[o];                                                     // :178
+        }
+      daq[j * nx + i] = (quad_avg_2d<N>(prod) * Re) * Re;                                   // :182,:185
+      dxq[j * nx + i] = quad_avg_1d<N>(sx + r0 * nuc + c0) * Re;                            // :183,:186
+    }
+    double col[N];
+#pragma unroll
+    for (int jj = 0; jj < N; ++jj) col[jj] = sy[(r0 + jj) * nuc + c0];
+    dyq[j * (nx + 1) + i] = quad_avg_1d<N>(col) * Re;                                       // :184,:187
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(128) k_quad_avg(const double* __restrict__ y, i64 m, double* __restrict__ out) {
+  const i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (e < m) out[e] = quad_avg_1d<N>(y + e * N);
+}
+template <int N>
+__global__ void __launch_bounds__(128) k_quad_avg2d(const double* __restrict__ y, i64 m, double* __restrict__ out) {
+  const i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (e >= m) return;
+  double v[N][N];
+#pragma unroll
+  for (int j = 0; j < N; ++j)
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[j][i] = y[e * N * N + j * N + i];
+  out[e] = quad_avg_2d<N>(v);
+}
+
+// ------------------------------------------------------------------------------------------------
+// displaced-pole cap (OGG:447-601)
+// ------------------------------------------------------------------------------------------------
+struct Cx { double re, im; };
+OGG_DI Cx cmul(Cx a, Cx b) { return Cx{a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }  // numpy, strict
+OGG_DI Cx cdivn(Cx a, Cx b) {  // numpy CDOUBLE_divide (Smith)
+  const double abr = fabs(b.re), abi = fabs(b.im);
+  Cx r;
+  if (abr >= abi) {
+    if (abr == 0 && abi == 0) { r.re = a.re / abr; r.im = a.im / abr; return r; }
+    const double rat = b.im / b.re;
+    const double scl = 1.0 / (b.re + b.im * rat);
+    r.re = (a.re + a.im * rat) * scl;
+    r.im = (a.im - a.re * rat) * scl;
+  } else {
+    const double rat = b.re / b.im;
+    const double scl = 1.0 / (b.im + b.re * rat);
+    r.re = (a.re * rat + a.im) * scl;
+    r.im = (a.im * rat - a.re) * scl;
+  }
+  return r;
+}
+OGG_DI Cx cis_np(double t) {  // cos(t) + 1j*sin(t) with numpy's promotions (:451,:495)
+  const SinCos q = sincos_parts(t);
+  const Cx js = cmul(Cx{0.0, 1.0}, Cx{sin_of(q), 0.0});
+  return Cx{cos_of(q) + js.re, 0.0 + js.im};
+}
+struct DpConst { double r_joint; Cx z0; };
+OGG_DI DpConst dp_load(const double* __restrict__ c) { return DpConst{c[0], Cx{c[1], c[2]}}; }
+
+OGG_DI Cx dp_col(double lon, Cx z0) {  // e2ithetaprime (:451-452), a function of longitude only
+  const Cx e = cis_np(lon * kPi180);
+  const Cx p = cmul(Cx{z0.re, -z0.im}, e);
+  return cdivn(Cx{e.re - z0.re, e.im - z0.im}, Cx{1.0 - p.re, 0.0 - p.im});
+}
+OGG_DI double dp_row(double lat, double r_joint) { return p_tan((90 + lat) * kPi180) / r_joint; }  // :448
+OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
+  const Cx z = cmul(Cx{r, 0.0}, ep);                                                         // :454
+  const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
+  const Cx w = cdivn(Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, 0.0 + q.im});        // :455
+  lam_raw = p_atan2(w.im, w.re) * (180.0 / kPi);                                             // :457
+  const double rw = sqrt(w.re * w.re + w.im * w.im);                                         // :465
+  phi = -90 + p_atan(rw * K.r_joint) / kPi180;                                               // :466
+}
+
+__global__ void k_dp_constants(double lat0, double lam_pole, double r_pole, double* __restrict__ out3) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    out3[0] = p_tan((90 + lat0) * kPi180);                                                   // :494
+    const Cx z0 = cmul(Cx{r_pole, 0.0}, cis_np(lam_pole * kPi180));                          // :495
+    out3[1] = z0.re;
+    out3[2] = z0.im;
+  }
+}
+__global__ void k_set3(double a, double b, double c, double* __restrict__ out3) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) { out3[0] = a; out3[1] = b; out3[2] = c; }
+}
+
+// raw (not yet unwrapped) projection of arbitrary 2-D input
+__global__ void __launch_bounds__(256) k_dp_projection_raw(const double* __restrict__ lon, const double* __restrict__ lat,
+                                                           i64 n, const double* __restrict__ cst,
+                                                           double* __restrict__ lam, double* __restrict__ phi) {
+  const DpConst K = dp_load(cst);
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x)
+    dp_vertex(dp_row(lat[e], K.r_joint), dp_col(lon[e], K.z0), K, lam[e], phi[e]);
+}
+
+// column / row tables for lattice evaluation: u = lon0 + (i*360)/ni (:479), v = -90 + (j*(lat0+90))/nj (:482)
+// `shift` is added to the index first (numerical_hi/hj pass i+eps etc., :538-558)
+__global__ void __launch_bounds__(256) k_dp_tables(const double* __restrict__ iv, i64 ncol, double ishift,
+                                                   const double* __restrict__ jv, i64 nrow, double jshift, i64 ni,
+                                                   i64 nj, double lon0, double lat0, const double* __restrict__ cst,
+                                                   Cx* __restrict__ ct, double* __restrict__ rt) {
+  const DpConst K = dp_load(cst);
+  const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (ct && t < ncol) {
+    const double idx = ishift != 0.0 ? iv[t] + ishift : iv[t];
+    ct[t] = dp_col(lon0 + (idx * 360.0) / (double)ni, K.z0);
+  }
+  if (rt && t < nrow) {
+    const double idx = jshift != 0.0 ? jv[t] + jshift : jv[t];
+    const double a = -90.0, b = lat0;
+    rt[t] = dp_row(a + (idx * (b - a)) / (double)nj, K.r_joint);
+  }
+}
+__global__ void __launch_bounds__(256) k_dp_lattice_raw(const Cx* __restrict__ ct, const double* __restrict__ rt,
+                                                        i64 nrow, i64 ncol, const double* __restrict__ cst,
+                                                        double* __restrict__ lam, double* __restrict__ phi) {
+  const i64 c = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  const DpConst K = dp_load(cst);
+  const Cx ep = ct[c];
+  for (i64 r = blockIdx.y; r < nrow; r += gridDim.y) dp_vertex(rt[r], ep, K, lam[r * ncol + c], phi[r * ncol + c]);
+}
+
+// --- monotonic_bounding (OGG:470-475) as a scan over 2-state maps ---------------------------------------
+// Element t with raw value x_t and predecessor raw value p.  If the predecessor ended up shifted its value is
+// fl(p - 360), else p.  m0 = [fl(x_t - p) > 100], m1 = [fl(x_t - fl(p - 360)) > 100] say whether t is shifted
+// given the predecessor's state; composition of such maps is associative, so one row is a prefix scan.
+// Up to 16 independent scans ("variants") are packed bitwise into one word.
+struct Map2 { unsigned f0, f1; };                      // image of state 0 / state 1, one bit per variant
+OGG_DI Map2 compose(Map2 first, Map2 then) {           // then o first
+  return Map2{(first.f0 & then.f1) | (~first.f0 & then.f0), (first.f1 & then.f1) | (~first.f1 & then.f0)};
+}
+OGG_DI unsigned apply_map(Map2 m, unsigned s) { return (s & m.f1) | (~s & m.f0); }
+
+// Block-wide inclusive scan; returns the state AFTER this thread's element given the tile's carry-in state.
+// sh: shared scratch of 2*kWarps+2 unsigned.  All threads of the block must call.
+template <int THREADS>
+OGG_DI unsigned tile_scan_states(Map2 m, unsigned s_in, unsigned* sh) {
+  constexpr int kWarps = THREADS / 32;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    Map2 e;
+    e.f0 = __shfl_up_sync(0xffffffffu, m.f0, off);
+    e.f1 = __shfl_up_sync(0xffffffffu, m.f1, off);
+    if (lane >= (unsigned)off) m = compose(e, m);
+  }
+  if (lane == 31u) { sh[2 * warp] = m.f0; sh[2 * warp + 1] = m.f1; }
+  __syncthreads();
+  unsigned s = s_in;
+  for (unsigned w = 0; w < warp; ++w) s = apply_map(Map2{sh[2 * w], sh[2 * w + 1]}, s);
+  const unsigned st = apply_map(m, s);
+  __syncthreads();  // sh may be reused by the caller / next tile
+  (void)kWarps;
+  return st;
+}
+
+constexpr int kScanThreads = 256;
+// in place on x[nj][ni]; x0 from x0_dev[0] if non-NULL (device scalar) else x0_host
+__global__ void __launch_bounds__(kScanThreads) k_monotonic(double* __restrict__ x, i64 nj, i64 ni, double x0_host,
+                                                            const double* __restrict__ x0_dev) {
+  __shared__ double raw[kScanThreads + 1];
+  __shared__ unsigned sh[2 * (kScanThreads / 32)];
+  __shared__ unsigned s_carry;
+  const double x0 = x0_dev ? x0_dev[0] : x0_host;
+  for (i64 j = blockIdx.x; j < nj; j += gridDim.x) {
+    double* row = x + j * ni;
+    if (threadIdx.x == 0) { raw[0] = row[0] * 0 + x0; s_carry = 0u; }  // x_im1 = x[:,0]*0 + x_0 (:471)
+    __syncthreads();
+    for (i64 t0 = 0; t0 < ni; t0 += kScanThreads) {
+      const i64 c = t0 + threadIdx.x;
+      const bool valid = c < ni;
+      const double v = valid ? row[c] : 0.0;
+      raw[threadIdx.x + 1] = v;
+      __syncthreads();
+      const double p = raw[threadIdx.x];
+      Map2 m{0u, 1u};  // identity for padding lanes
+      if (valid) { m.f0 = (v - p) > 100 ? 1u : 0u; m.f1 = (v - (p - 360)) > 100 ? 1u : 0u; }
+      const unsigned s_in = s_carry;
+      const unsigned st = tile_scan_states<kScanThreads>(m, s_in, sh);
+      if (valid) row[c] = (st & 1u) ? v - 360 : v;                       // :473
+      const i64 last = (ni - t0 < kScanThreads ? ni - t0 : kScanThreads) - 1;
+      if ((i64)threadIdx.x == last) { raw[0] = v; s_carry = st; }
+      __syncthreads();
+    }
+  }
+}
+
+// great_arc_distance tail (OGG:527-532) on two projected meshes
+OGG_DI double haversine(double lam0, double phi0, double lam1, double phi1) {
+  const double l0 = lam0 * kPi180, p0 = phi0 * kPi180, l1 = lam1 * kPi180, p1 = phi1 * kPi180;
+  const double dphi = p1 - p0, dlam = l1 - l0;
+  const double s1 = p_sin(0.5 * dphi), s2 = p_sin(0.5 * dlam);
+  const double d = s1 * s1 + ((s2 * s2) * p_cos(p0)) * p_cos(p1);  // :531
+  return 2.0 * p_asin(sqrt(d));                                    // :532
+}
+__global__ void __launch_bounds__(256) k_haversine(const double* __restrict__ lam0, const double* __restrict__ phi0,
+                                                   const double* __restrict__ lam1, const double* __restrict__ phi1,
+                                                   i64 n, double* __restrict__ out) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x)
+    out[e] = haversine(lam0[e], phi0[e], lam1[e], phi1[e]);
+}
+template <int ORDER>
+OGG_DI double fd_combine(double ds2, double ds4, double ds6, double reps) {  // :539-546
+  if (ORDER == 2) return (0.5 * ds2) * reps;
+  if (ORDER == 4) return ((8.0 * ds2 - ds4) * (1.0 / 12.0)) * reps;
+  return (((45.0 * ds2 - 9.0 * ds4) + ds6) * (1.0 / 60.0)) * reps;
+}
+__global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ ds2, const double* __restrict__ ds4,
+                                                    const double* __restrict__ ds6, int order, double reps, i64 n,
+                                                    double* __restrict__ out) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    if (order == 2) out[e] = fd_combine<2>(ds2[e], 0, 0, reps);
+    else if (order == 4) out[e] = fd_combine<4>(ds2[e], ds4[e], 0, reps);
+    else out[e] = fd_combine<6>(ds2[e], ds4[e], ds6[e], reps);
+  }
+}
+
+// --- fused numerical_hi + numerical_hj on a lattice of unique samples (OGG:583-584) ------------------------------
+// One block per sample row sweeping the row in tiles of kScanThreads columns.  For finite-difference order
+// 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column), each needing its own
+// longitude unwrap along the row: their 2-state maps are packed into one word and scanned together; the
+// carry (previous raw longitude and shift state per mesh) moves from tile to tile through shared memory.
+// Column table ct: [ncol][1+2NV] = e' at {i, i+eps, i-eps, i+2eps, i-2eps, ...}; row table rt: [nrow][1+2NV] likewise.
+template <int NV>
+__global__ void __launch_bounds__(kScanThreads) k_dp_hsamples(const Cx* __restrict__ ct, const double* __restrict__ rt,
+                                                              i64 nrow, i64 ncol, const double* __restrict__ x0v,
+                                                              const double* __restrict__ cst, double reps,
+                                                              double* __restrict__ hx, double* __restrict__ hy) {
+  constexpr int NM = 4 * NV;       // meshes
+  constexpr int NT = 1 + 2 * NV;   // table entries per row / column
+  __shared__ double raw[NM][kScanThreads + 1];
+  __shared__ unsigned sh[2 * (kScanThreads / 32)];
+  __shared__ unsigned s_carry;
+  __shared__ double rrow[NT];
+  const DpConst K = dp_load(cst);
+  for (i64 r = blockIdx.x; r < nrow; r += gridDim.x) {
+    if (threadIdx.x < NT) rrow[threadIdx.x] = rt[r * NT + threadIdx.x];
+    if (threadIdx.x < NM) raw[threadIdx.x][0] = x0v[threadIdx.x];  // x_0 = lon_grid[0,0] of that mesh
+    if (threadIdx.x == 0) s_carry = 0u;
+    __syncthreads();
+    for (i64 t0 = 0; t0 < ncol; t0 += kScanThreads) {
+      const i64 c = t0 + threadIdx.x;
+      const bool valid = c < ncol;
+      double lam[NM], phi[NM];
+      if (valid) {
+        const Cx* cc = ct + c * NT;
+        const Cx e0 = cc[0];
+#pragma unroll
+        for (int m = 0; m < NV; ++m) {
+          dp_vertex(rrow[0], cc[1 + 2 * m], K, lam[4 * m + 0], phi[4 * m + 0]);      // (j, i+(m+1)eps)
+          dp_vertex(rrow[0], cc[2 + 2 * m], K, lam[4 * m + 1], phi[4 * m + 1]);      // (j, i-(m+1)eps)
+          dp_vertex(rrow[1 + 2 * m], e0, K, lam[4 * m + 2], phi[4 * m + 2]);         // (j+(m+1)eps, i)
+          dp_vertex(rrow[2 + 2 * m], e0, K, lam[4 * m + 3], phi[4 * m + 3]);         // (j-(m+1)eps, i)
+        }
+      } else {
+#pragma unroll
+        for (int m = 0; m < NM; ++m) { lam[m] = 0.0; phi[m] = 0.0; }
+      }
+#pragma unroll
+      for (int m = 0; m < NM; ++m) raw[m][threadIdx.x + 1] = lam[m];
+      __syncthreads();
+      Map2 mp{0u, 0u};
+      if (valid) {
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+          const double p = raw[m][threadIdx.x];
+          mp.f0 |= ((lam[m] - p) > 100 ? 1u : 0u) << m;
+          mp.f1 |= ((lam[m] - (p - 360)) > 100 ? 1u : 0u) << m;
+        }
+      } else {
+        mp.f0 = 0u; mp.f1 = 0xffffffffu;
+      }
+      const unsigned s_in = s_carry;
+      const unsigned st = tile_scan_states<kScanThreads>(mp, s_in, sh);
+      const i64 last = (ncol - t0 < kScanThreads ? ncol - t0 : kScanThreads) - 1;
+      if ((i64)threadIdx.x == last) {
+#pragma unroll
+        for (int m = 0; m < NM; ++m) raw[m][0] = lam[m];
+        s_carry = st;
+      }
+      if (valid) {
+#pragma unroll
+        for (int m = 0; m < NM; ++m)
+          if ((st >> m) & 1u) lam[m] = lam[m] - 360;                                 // :473
+        double dsi[3] = {0, 0, 0}, dsj[3] = {0, 0, 0};
+#pragma unroll
+        for (int m = 0; m < NV; ++m) {
+          // great_arc_distance(j, i+s, j, i-s): mesh0 = plus, mesh1 = minus (:538,:541,:544)
+          dsi[m] = haversine(lam[4 * m + 0], phi[4 * m + 0], lam[4 * m + 1], phi[4 * m + 1]);
+          dsj[m] = haversine(lam[4 * m + 2], phi[4 * m + 2], lam[4 * m + 3], phi[4 * m + 3]);
+        }
+        hx[r * ncol + c] = fd_combine<2 * NV>(dsi[0], dsi[1], dsi[2], reps);
+        hy[r * ncol + c] = fd_combine<2 * NV>(dsj[0], dsj[1], dsj[2], reps);
+      }
+      __syncthreads();
+    }
+  }
+}
+// x_0 of every shifted mesh: lon0 + ((i[0] (+/-) s)*360)/ni  (:463 with :479)
+template <int NV>
+__global__ void k_dp_x0(const double* __restrict__ iv, double eps, i64 ni, double lon0, double* __restrict__ x0v) {
+  const int m = threadIdx.x;
+  if (m >= 4 * NV) return;
+  const int lvl = m / 4, kind = m % 4;
+  const double s = lvl == 0 ? eps : (lvl == 1 ? 2.0 * eps : 3.0 * eps);
+  double idx = iv[0];
+  if (kind == 0) idx = iv[0] + s;
+  if (kind == 1) idx = iv[0] - s;
+  x0v[m] = lon0 + (idx * 360.0) / (double)ni;
+}
+
+// ------------------------------------------------------------------------------------------------
+// reductions
+// ------------------------------------------------------------------------------------------------
+constexpr int kRedThreads = 256;
+constexpr int kRedBlocks = 592;  // 4 x 148
+OGG_DI double block_sum(double v, double* sh) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (warp == 0) {
+    t = lane < kRedThreads / 32 ? sh[lane] : 0.0;
+#pragma unroll
+    for (int off = 4; off > 0; off >>= 1) t += __shfl_down_sync(0xffffffffu, t, off);
+  }
+  return t;  // valid in thread 0
+}
+__global__ void __launch_bounds__(kRedThreads) k_sum_partial(const double* __restrict__ a, i64 n, i64 stride,
+                                                             double* __restrict__ partial) {
+  __shared__ double sh[kRedThreads / 32];
+  double v = 0.0;
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) v += a[e * stride];
+  const double t = block_sum(v, sh);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+__global__ void __launch_bounds__(kRedThreads) k_sum_final(const double* __restrict__ partial, int np,
+                                                           double* __restrict__ out) {
+  __shared__ double sh[kRedThreads / 32];
+  double v = 0.0;
+  for (int e = threadIdx.x; e < np; e += blockDim.x) v += partial[e];
+  const double t = block_sum(v, sh);
+  if (threadIdx.x == 0) out[0] = t;
+}
+
+// FP64 issue-rate probe: 8 independent chains of dependent (mul, add) pairs
+__global__ void __launch_bounds__(256) k_fp64_rate(i64 iters, double seed, double* __restrict__ sink) {
+  double a[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = seed + (double)(threadIdx.x + k);
+  const double m = 1.0000001, c = 1e-9;
+  for (i64 it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = a[k] * m + c;  // -fmad=false: DMUL + DADD
+  }
+  double s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += a[k];
+  if (s == 12345.678) sink[0] = s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side composition helpers
+// ------------------------------------------------------------------------------------------------
+static dim3 lattice_grid(i64 ncol, i64 nrow, int threads) {
+  const unsigned gx = cdiv_u(ncol, threads);
+  i64 gy = ((i64)num_sms() * 16 + gx - 1) / gx;
+  if (gy > nrow) gy = nrow;
+  if (gy < 1) gy = 1;
+  if (gy > 65535) gy = 65535;
+  return dim3(gx, (unsigned)gy, 1);
+}
+
+template <typename KERN, typename... Args>
+static int launch_quad(int order, KERN k2, KERN k3, KERN k4, KERN k5, dim3 g, dim3 b, cudaStream_t st, Args... args) {
+  if (order == 2) k2<<<g, b, 0, st>>>(args...);
+  else if (order == 3) k3<<<g, b, 0, st>>>(args...);
+  else if (order == 4) k4<<<g, b, 0, st>>>(args...);
+  else k5<<<g, b, 0, st>>>(args...);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+static int run_quad_cells(int order, const double* sx, const double* sy, i64 nuc, i64 ncr, i64 nx, i64 top_row,
+                          double Re, double* dxq, double* dyq, double* daq, cudaStream_t st) {
+  dim3 g = lattice_grid(nx + 1, ncr + 1, 128);
+  return launch_quad(order, k_quad_cells<2>, k_quad_cells<3>, k_quad_cells<4>, k_quad_cells<5>, g, dim3(128), st, sx, sy,
+                     nuc, ncr, nx, top_row, Re, dxq, dyq, daq);
+}
+
+// cap on the per-chunk sample scratch of the quadrature drivers (bytes of dx+dy samples)
+static const i64 kQuadChunkBytes = (i64)1 << 30;
+
+static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow, i64 ni, i64 nj, double lon0,
+                         double lat0, const double* cst, int nv, double eps, Cx* ct, double* rt, cudaStream_t st);
+
+}  // namespace ogg
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+using namespace ogg;
+
+extern "C" {
+
+const char* ogg_version(void) { return "ogg_b200 0.1 (sm_100a, fp64, fmad=false)"; }
+
+int ogg_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int ogg_sin(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_SIN>(in, out, n, s); }
+int ogg_cos(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_COS>(in, out, n, s); }
+int ogg_tan(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_TAN>(in, out, n, s); }
+int ogg_arcsin(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_ASIN>(in, out, n, s); }
+int ogg_arccos(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_ACOS>(in, out, n, s); }
+int ogg_arctan(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_ATAN>(in, out, n, s); }
+int ogg_exp(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_EXP>(in, out, n, s); }
+int ogg_log(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_LOG>(in, out, n, s); }
+int ogg_sinh(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_SINH>(in, out, n, s); }
+int ogg_cosh(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_COSH>(in, out, n, s); }
+int ogg_mod360(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_MOD360>(in, out, n, s); }
+int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* stream) {
+  if (n < 0 || (n > 0 && (!y || !x || !out))) return OGG_ERR_ARG;
+  if (n == 0) return OGG_OK;
+  k_atan2<<<flat_grid(n), 256, 0, S(stream)>>>(y, x, out, n);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int64_t nxp, double Re, int flags,
+                          double* x, double* y, double* dx, double* dy, double* area, double* angle, void* stream) {
+  if (!lam || !phi || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  double *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
+  OGG_CUDA(ws.get(&dxi, nxp)); OGG_CUDA(ws.get(&hx, nxp)); OGG_CUDA(ws.get(&xd, nxp));
+  OGG_CUDA(ws.get(&cl, nyp)); OGG_CUDA(ws.get(&cy, nyp)); OGG_CUDA(ws.get(&dyr, nyp)); OGG_CUDA(ws.get(&dsl, nyp));
+  const i64 m = nxp > nyp ? nxp : nyp;
+  k_band_tables<<<cdiv_u(m, 256), 256, 0, st>>>(lam, phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
+  OGG_LAUNCH_CHECK();
+  const i64 nyp_v = (flags & OGG_BAND_SKIP_TOP_VERTEX_ROW) ? nyp - 1 : nyp;
+  const int metrics = (flags & OGG_BAND_NO_METRICS) ? 0 : 1;
+  dim3 g(cdiv_u(nxp, 256), cdiv_u(nyp, kBandRows));
+  k_band_fill<<<g, 256, 0, st>>>(lam, phi, dxi, hx, xd, cl, cy, dyr, dsl, nyp, nxp, nyp_v, Re, Re * Re, metrics, x, y, dx,
+                                 dy, area, angle);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp, double Re, int areafix,
+                      const double* halo_x, const double* halo_y, double* dx, double* dy, double* area, void* stream) {
+  if (!x || !y || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
+  if ((halo_x == nullptr) != (halo_y == nullptr)) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  const i64 nrows = nyp + (halo_x ? 1 : 0);
+  dim3 g(cdiv_u(nxp, 128), cdiv_u(nrows, kMidasRows));
+  k_midas<<<g, 128, 0, st>>>(x, y, nyp, nxp, Re, Re * Re, areafix, halo_x, halo_y, dx, dy, area);
+  OGG_LAUNCH_CHECK();
+  if (!areafix && area) {
+    if (!dx || !dy) return OGG_ERR_ARG;
+    const i64 ny = nrows - 1, nx = nxp - 1;
+    if (ny > 0) {
+      Scratch ws(st);
+      double* top = nullptr;
+      if (halo_x) {
+        OGG_CUDA(ws.get(&top, nx));
+        k_dx_row<<<cdiv_u(nx, 256), 256, 0, st>>>(halo_x, halo_y, nx, Re, top);
+        OGG_LAUNCH_CHECK();
+      }
+      k_area_nofix<<<flat_grid(ny * nx), 256, 0, st>>>(dx, top, dy, ny, nx, area);
+      OGG_LAUNCH_CHECK();
+    }
+  }
+  return OGG_OK;
+}
+
+int ogg_angle_x(const double* x, const double* y, int64_t nyp, int64_t nxp, double* angle, void* stream) {
+  if (!x || !y || !angle || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
+  k_angle<<<lattice_grid(nxp, nyp, 256), 256, 0, S(stream)>>>(x, y, nyp, nxp, angle);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_bipolar_projection(const double* lamg, const double* phig, int64_t n, double lon_bp, double rp, int metrics_only,
+                           double* lams, double* phis, double* hi, double* hj, void* stream) {
+  if (n < 0 || (n > 0 && (!lamg || !phig))) return OGG_ERR_ARG;
+  if (!metrics_only && (!lams || !phis)) return OGG_ERR_ARG;
+  if (n == 0) return OGG_OK;
+  k_bp_projection<<<flat_grid(n), 256, 0, S(stream)>>>(lamg, phig, n, lon_bp, rp, metrics_only, lams, phis, hi, hj);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_bipolar_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lat0_bp, double lon_bp, double rp,
+                         double* lams, double* phis, double* h_i_inv, double* h_j_inv, void* stream) {
+  if (Ni < 1 || Nj < 1 || j0 < 0 || j1 > Nj + 1 || j0 >= j1 || !lams || !phis) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  const i64 ncol = Ni + 1, nrow = j1 - j0;
+  BpCol* ct; BpRow* rt;
+  OGG_CUDA(ws.get(&ct, ncol)); OGG_CUDA(ws.get(&rt, nrow));
+  const i64 m = ncol > nrow ? ncol : nrow;
+  k_bp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(nullptr, 0, ncol, nullptr, j0, nrow, Ni, Nj, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH_CHECK();
+  k_bp_lattice<0><<<lattice_grid(ncol, nrow, 256), 256, 0, st>>>(ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
+                                                                 phis, h_i_inv, h_j_inv);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64_t nj, int64_t Ni, int64_t Nj_ncap,
+                             double lat0_bp, double lon_bp, double rp, double* h_i_inv, double* h_j_inv, void* stream) {
+  if (!i || !j || ni < 1 || nj < 1 || !h_i_inv || !h_j_inv) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  BpCol* ct; BpRow* rt;
+  OGG_CUDA(ws.get(&ct, ni)); OGG_CUDA(ws.get(&rt, nj));
+  const i64 m = ni > nj ? ni : nj;
+  k_bp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(i, 0, ni, j, 0, nj, Ni, Nj_ncap, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH_CHECK();
+  k_bp_lattice<1><<<lattice_grid(ni, nj, 256), 256, 0, st>>>(ct, rt, nj, ni, Ni, Nj_ncap, 0, lat0_bp, lon_bp, rp, h_i_inv,
+                                                             h_j_inv, nullptr, nullptr);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lat0_bp, double lon_bp,
+                                 double rp, double Re, double* dxq, double* dyq, double* daq, void* stream) {
+  QuadNodes q;
+  if (quad_nodes_host(order, &q)) return OGG_ERR_UNCODED_ORDER;
+  if (nx < 1 || ny < 1 || j0 < 0 || j1 > ny || j0 >= j1 || !dxq || !dyq || !daq) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  const i64 nuc = (order - 1) * nx + 1;
+  i64 rows_per_chunk = kQuadChunkBytes / (16 * nuc * (order - 1));
+  if (rows_per_chunk < 1) rows_per_chunk = 1;
+  Scratch ws(st);
+  const i64 max_cr = rows_per_chunk < (j1 - j0) ? rows_per_chunk : (j1 - j0);
+  const i64 max_nur = (order - 1) * max_cr + 2;
+  double *iv, *jv, *sx, *sy;
+  BpCol* ct; BpRow* rt;
+  OGG_CUDA(ws.get(&iv, nuc)); OGG_CUDA(ws.get(&jv, max_nur));
+  OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, max_nur));
+  OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
+  k_sample_index<<<cdiv_u(nuc + 1, 256), 256, 0, st>>>(q, order, 0, nx, nx, 0, iv);
+  OGG_LAUNCH_CHECK();
+  k_bp_tables<<<cdiv_u(nuc, 256), 256, 0, st>>>(iv, 0, nuc, nullptr, 0, 0, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH_CHECK();
+  for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
+    const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
+    const bool top = c1 == ny;
+    const i64 nur = (order - 1) * (c1 - c0) + 1 + (top ? 1 : 0);
+    k_sample_index<<<cdiv_u(nur + 1, 256), 256, 0, st>>>(q, order, c0, c1, ny, 1, jv);   // :144-151
+    OGG_LAUNCH_CHECK();
+    k_bp_tables<<<cdiv_u(nur, 256), 256, 0, st>>>(nullptr, 0, 0, jv, 0, nur, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
+    OGG_LAUNCH_CHECK();
+    k_bp_lattice<1><<<lattice_grid(nuc, nur, 256), 256, 0, st>>>(ct, rt, nur, nuc, nx, ny, 0, lat0_bp, lon_bp, rp, sx, sy,
+                                                                 nullptr, nullptr);
+    OGG_LAUNCH_CHECK();
+    int rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
+                            dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
+    if (rc) return rc;
+  }
+  return OGG_OK;
+}
+
+int ogg_quad_positions(int n, double* a, double* b) {
+  QuadNodes q;
+  if (quad_nodes_host(n, &q)) return OGG_ERR_UNCODED_ORDER;
+  for (int k = 0; k < n; ++k) { a[k] = q.a[k]; b[k] = q.b[k]; }
+  return OGG_OK;
+}
+int ogg_quad_average(const double* y, int64_t m, int n, double* out, void* stream) {
+  if (n < 2 || n > 5) return OGG_ERR_UNCODED_ORDER;
+  if (m < 1 || !y || !out) return OGG_ERR_ARG;
+  return launch_quad(n, k_quad_avg<2>, k_quad_avg<3>, k_quad_avg<4>, k_quad_avg<5>, dim3(cdiv_u(m, 128)), dim3(128),
+                     S(stream), y, (i64)m, out);
+}
+int ogg_quad_average_2d(const double* y, int64_t m, int n, double* out, void* stream) {
+  if (n < 2 || n > 5) return OGG_ERR_UNCODED_ORDER;
+  if (m < 1 || !y || !out) return OGG_ERR_ARG;
+  return launch_quad(n, k_quad_avg2d<2>, k_quad_avg2d<3>, k_quad_avg2d<4>, k_quad_avg2d<5>, dim3(cdiv_u(m, 128)),
+                     dim3(128), S(stream), y, (i64)m, out);
+}
+
+int ogg_dp_constants(double lat0, double lam_pole, double r_pole, double* out3, void* stream) {
+  if (!out3) return OGG_ERR_ARG;
+  k_dp_constants<<<1, 32, 0, S(stream)>>>(lat0, lam_pole, r_pole, out3);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_monotonic_bounding(double* x, int64_t nj, int64_t ni, double x_0, void* stream) {
+  if (!x || nj < 1 || ni < 1) return OGG_ERR_ARG;
+  const i64 cap = (i64)num_sms() * 8;
+  k_monotonic<<<(unsigned)(nj < cap ? nj : cap), kScanThreads, 0, S(stream)>>>(x, nj, ni, x_0, nullptr);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_dp_projection(const double* lon, const double* lat, int64_t nj, int64_t ni, double z0_re, double z0_im,
+                      double r_joint, double* lam, double* phi, void* stream) {
+  if (!lon || !lat || !lam || !phi || nj < 1 || ni < 1) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  double* cst;
+  OGG_CUDA(ws.get(&cst, 3));
+  k_set3<<<1, 32, 0, st>>>(r_joint, z0_re, z0_im, cst);
+  OGG_LAUNCH_CHECK();
+  k_dp_projection_raw<<<flat_grid(nj * ni), 256, 0, st>>>(lon, lat, nj * ni, cst, lam, phi);
+  OGG_LAUNCH_CHECK();
+  const i64 cap = (i64)num_sms() * 8;
+  k_monotonic<<<(unsigned)(nj < cap ? nj : cap), kScanThreads, 0, st>>>(lam, nj, ni, 0.0, lon);  // x_0 = lon_grid[0,0] (:463)
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+}  // extern "C"
+
+namespace ogg {
+// single shifted mesh on index vectors: tables -> raw lattice -> unwrap.  cst: device {r_joint, z0}
+static int dp_mesh_dev(const double* iv, i64 nil, double ishift, const double* jv, i64 njl, double jshift, i64 ni, i64 nj,
+                       double lon0, double lat0, const double* cst, double* lams, double* phis, cudaStream_t st) {
+  Scratch ws(st);
+  Cx* ct; double* rt; double* x0;
+  OGG_CUDA(ws.get(&ct, nil)); OGG_CUDA(ws.get(&rt, njl)); OGG_CUDA(ws.get(&x0, 12));
+  const i64 m = nil > njl ? nil : njl;
+  k_dp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(iv, nil, ishift, jv, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
+  OGG_LAUNCH_CHECK();
+  k_dp_lattice_raw<<<lattice_grid(nil, njl, 256), 256, 0, st>>>(ct, rt, njl, nil, cst, lams, phis);
+  OGG_LAUNCH_CHECK();
+  // x_0 = lon_grid[0,0] = lon0 + ((i[0]+shift)*360)/ni : reuse k_dp_x0<1> slots (kind 0 = plus shift, kind 2 = none)
+  k_dp_x0<1><<<1, 32, 0, st>>>(iv, ishift, ni, lon0, x0);
+  OGG_LAUNCH_CHECK();
+  const i64 cap = (i64)num_sms() * 8;
+  k_monotonic<<<(unsigned)(njl < cap ? njl : cap), kScanThreads, 0, st>>>(lams, njl, nil, 0.0, ishift != 0.0 ? x0 + 0 : x0 + 2);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+}  // namespace ogg
+
+extern "C" {
+
+int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int64_t ni, int64_t nj, double lon0, double lat0,
+                double lam_pole, double r_pole, double* lams, double* phis, void* stream) {
+  if (!i || !j || nil < 1 || njl < 1 || !lams || !phis) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  double* cst;
+  OGG_CUDA(ws.get(&cst, 3));
+  k_dp_constants<<<1, 32, 0, st>>>(lat0, lam_pole, r_pole, cst);
+  OGG_LAUNCH_CHECK();
+  return dp_mesh_dev(i, nil, 0.0, j, njl, 0.0, ni, nj, lon0, lat0, cst, lams, phis, st);
+}
+
+int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl, int64_t nil,
+                           int64_t nx, int64_t ny, double lon0, double lat0, double lon_dp, double r_dp, double* out,
+                           void* stream) {
+  if (!j0 || !i0 || !j1 || !i1 || !out || njl < 1 || nil < 1) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  const i64 n = njl * nil;
+  double *cst, *l0, *p0, *l1, *p1;
+  OGG_CUDA(ws.get(&cst, 3));
+  OGG_CUDA(ws.get(&l0, n)); OGG_CUDA(ws.get(&p0, n)); OGG_CUDA(ws.get(&l1, n)); OGG_CUDA(ws.get(&p1, n));
+  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH_CHECK();
+  int rc = dp_mesh_dev(i0, nil, 0.0, j0, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
+  if (rc) return rc;
+  rc = dp_mesh_dev(i1, nil, 0.0, j1, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
+  if (rc) return rc;
+  k_haversine<<<flat_grid(n), 256, 0, st>>>(l0, p0, l1, p1, n, out);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+}  // extern "C"
+
+namespace ogg {
+// tables for the fused h-sample kernel: ct [ncol][1+2nv], rt [nrow][1+2nv] (centre, +eps, -eps, +2eps, -2eps, ...)
+__global__ void __launch_bounds__(256) k_dp_tables_multi(const double* __restrict__ iv, i64 ncol,
+                                                         const double* __restrict__ jv, i64 nrow, i64 ni, i64 nj,
+                                                         double lon0, double lat0, const double* __restrict__ cst, int nv,
+                                                         double eps, Cx* __restrict__ ct, double* __restrict__ rt) {
+  const DpConst K = dp_load(cst);
+  const int nt = 1 + 2 * nv;
+  const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  for (int k = 0; k < nt; ++k) {
+    const int lvl = (k + 1) / 2;  // 0 centre, 1: eps, 2: 2eps, 3: 3eps
+    const double s = lvl == 1 ? eps : (lvl == 2 ? 2.0 * eps : 3.0 * eps);
+    const bool plus = (k & 1) == 1;
+    if (ct && t < ncol) {
+      const double idx = k == 0 ? iv[t] : (plus ? iv[t] + s : iv[t] - s);            // :538,:541,:544
+      ct[t * nt + k] = dp_col(lon0 + (idx * 360.0) / (double)ni, K.z0);
+    }
+    if (rt && t < nrow) {
+      const double idx = k == 0 ? jv[t] : (plus ? jv[t] + s : jv[t] - s);            // :553,:556,:559
+      const double a = -90.0, b = lat0;
+      rt[t * nt + k] = dp_row(a + (idx * (b - a)) / (double)nj, K.r_joint);
+    }
+  }
+}
+static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow, i64 ni, i64 nj, double lon0, double lat0,
+                         const double* cst, int nv, double eps, Cx* ct, double* rt, cudaStream_t st) {
+  const i64 m = (ct ? ncol : 0) > (rt ? nrow : 0) ? (ct ? ncol : 0) : (rt ? nrow : 0);
+  if (m == 0) return OGG_OK;
+  k_dp_tables_multi<<<cdiv_u(m, 256), 256, 0, st>>>(iv, ncol, jv, nrow, ni, nj, lon0, lat0, cst, nv, eps, ct, rt);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
+                       double reps, double* hx, double* hy, cudaStream_t st) {
+  const i64 cap = (i64)num_sms() * 4;
+  const unsigned g = (unsigned)(nrow < cap ? nrow : cap);
+  if (nv == 1) k_dp_hsamples<1><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  else if (nv == 2) k_dp_hsamples<2><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  else k_dp_hsamples<3><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
+  if (nv == 1) k_dp_x0<1><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
+  else if (nv == 2) k_dp_x0<2><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
+  else k_dp_x0<3><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+}  // namespace ogg
+
+extern "C" {
+
+int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i, int64_t nil, int64_t nx, int64_t ny,
+                    double lon0, double lat0, double lon_dp, double r_dp, double eps, int order, double* out, void* stream) {
+  if (!j || !i || !out || njl < 1 || nil < 1 || (direction != 0 && direction != 1)) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  // the reference evaluates ds2 (and ds4, ds6) before it finds the order uncoded (:538-547); only the status matters here
+  const int nds = order == 2 ? 1 : (order == 4 ? 2 : (order == 6 ? 3 : 0));
+  if (nds == 0) return OGG_ERR_ORDER_NOT_CODED;
+  Scratch ws(st);
+  const i64 n = njl * nil;
+  double *cst, *l0, *p0, *l1, *p1, *ds[3] = {nullptr, nullptr, nullptr};
+  OGG_CUDA(ws.get(&cst, 3));
+  OGG_CUDA(ws.get(&l0, n)); OGG_CUDA(ws.get(&p0, n)); OGG_CUDA(ws.get(&l1, n)); OGG_CUDA(ws.get(&p1, n));
+  for (int m = 0; m < nds; ++m) OGG_CUDA(ws.get(&ds[m], n));
+  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH_CHECK();
+  for (int m = 0; m < nds; ++m) {
+    const double s = m == 0 ? eps : (m == 1 ? 2.0 * eps : 3.0 * eps);
+    int rc;
+    if (direction == 0) {
+      rc = dp_mesh_dev(i, nil, s, j, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
+      if (!rc) rc = dp_mesh_dev(i, nil, -s, j, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
+    } else {
+      rc = dp_mesh_dev(i, nil, 0.0, j, njl, s, nx, ny, lon0, lat0, cst, l0, p0, st);
+      if (!rc) rc = dp_mesh_dev(i, nil, 0.0, j, njl, -s, nx, ny, lon0, lat0, cst, l1, p1, st);
+    }
+    if (rc) return rc;
+    k_haversine<<<flat_grid(n), 256, 0, st>>>(l0, p0, l1, p1, n, ds[m]);
+    OGG_LAUNCH_CHECK();
+  }
+  k_fd_combine<<<flat_grid(n), 256, 0, st>>>(ds[0], ds[1], ds[2], order, 1.0 / eps, n, out);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lon0, double lat0, double lon_dp,
+                        double r_dp, double Re, double* dxq, double* dyq, double* daq, void* stream) {
+  QuadNodes q;
+  if (quad_nodes_host(order, &q)) return OGG_ERR_UNCODED_ORDER;      // quad_positions raises first (:567)
+  if (order != 2 && order != 4) return OGG_ERR_ORDER_NOT_CODED;      // numerical_hi(order=order) (:583)
+  if (nx < 1 || ny < 1 || j0 < 0 || j1 > ny || j0 >= j1 || !dxq || !dyq || !daq) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  const int nv = order / 2, nt = 1 + 2 * nv;
+  const double eps = 1e-3;                                           // :583-584
+  const i64 nuc = (order - 1) * nx + 1;
+  i64 rows_per_chunk = kQuadChunkBytes / (16 * nuc * (order - 1));
+  if (rows_per_chunk < 1) rows_per_chunk = 1;
+  const i64 max_cr = rows_per_chunk < (j1 - j0) ? rows_per_chunk : (j1 - j0);
+  const i64 max_nur = (order - 1) * max_cr + 2;
+  Scratch ws(st);
+  double *cst, *iv, *jv, *rt, *x0v, *sx, *sy;
+  Cx* ct;
+  OGG_CUDA(ws.get(&cst, 3)); OGG_CUDA(ws.get(&iv, nuc + 1)); OGG_CUDA(ws.get(&jv, max_nur));
+  OGG_CUDA(ws.get(&ct, nuc * nt)); OGG_CUDA(ws.get(&rt, max_nur * nt)); OGG_CUDA(ws.get(&x0v, 12));
+  OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
+  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH_CHECK();
+  k_sample_index<<<cdiv_u(nuc + 1, 256), 256, 0, st>>>(q, order, 0, nx, nx, 0, iv);       // :578-581
+  OGG_LAUNCH_CHECK();
+  int rc = dp_tables_for(iv, nuc, nullptr, 0, nx, ny, lon0, lat0, cst, nv, eps, ct, nullptr, st);
+  if (rc) return rc;
+  rc = dp_x0(nv, iv, eps, nx, lon0, x0v, st);
+  if (rc) return rc;
+  for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
+    const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
+    const bool top = c1 == ny;
+    const i64 nur = (order - 1) * (c1 - c0) + 1;                                           // closing row = row ny when top
+    k_sample_index<<<cdiv_u(nur + 1, 256), 256, 0, st>>>(q, order, c0, c1, ny, 0, jv);    // :573-576
+    OGG_LAUNCH_CHECK();
+    rc = dp_tables_for(nullptr, 0, jv, nur, nx, ny, lon0, lat0, cst, nv, eps, nullptr, rt, st);
+    if (rc) return rc;
+    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, st);
+    if (rc) return rc;
+    rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
+                        dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
+    if (rc) return rc;
+  }
+  return OGG_OK;
+}
+
+int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, void* stream) {
+  if (!a || !out || n < 0 || stride < 1) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  double* partial;
+  OGG_CUDA(ws.get(&partial, kRedBlocks));
+  k_sum_partial<<<kRedBlocks, kRedThreads, 0, st>>>(a, n, stride, partial);
+  OGG_LAUNCH_CHECK();
+  k_sum_final<<<1, kRedThreads, 0, st>>>(partial, kRedBlocks, out);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_fp64_issue_rate(int64_t iters, double* ginstr_per_s_host) {
+  if (!ginstr_per_s_host || iters < 1) return OGG_ERR_ARG;
+  double* sink;
+  OGG_CUDA(cudaMalloc(&sink, 8));
+  cudaEvent_t e0, e1;
+  OGG_CUDA(cudaEventCreate(&e0)); OGG_CUDA(cudaEventCreate(&e1));
+  const int blocks = num_sms() * 8;
+  k_fp64_rate<<<blocks, 256>>>(iters / 8 + 1, 1.0, sink);  // warm-up
+  OGG_CUDA(cudaEventRecord(e0));
+  k_fp64_rate<<<blocks, 256>>>(iters, 1.0, sink);
+  OGG_CUDA(cudaEventRecord(e1));
+  OGG_CUDA(cudaEventSynchronize(e1));
+  float ms = 0;
+  OGG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  const double instr = (double)blocks * 256.0 * (double)iters * 16.0;
+  *ginstr_per_s_host = instr / (ms * 1e-3) / 1e9;
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+  return OGG_OK;
+}
+
+}  // extern "C"

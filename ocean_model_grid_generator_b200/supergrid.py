@@ -1,0 +1,434 @@
+"""Plan + in-place device build of the stitched supergrid (the body of the reference's main(), OGG:855-1449).
+
+Host side (this file): the reference's sizing rules, cuts and joins reduced to a *plan* -- an ordered list of
+sub-grid pieces (south to north) with their generator parameters, the rows kept, and the row offset each piece
+is written at.  Device side: every piece is generated straight into the six final arrays at its offset
+(no sub-grid temporaries, no concatenate copies -- OGG:1316-1365 becomes pointer arithmetic), optionally only a
+latitude row-slab of each piece (one slab per GPU).
+
+Joins follow OGG:1316-1365: x, y, dx, angle_dx = lower[:-1] + upper;  dy, area = lower + upper.
+"""
+import sys
+import time
+
+import numpy
+
+from . import _cabi
+from . import device as _dev
+from . import devnp as np
+from . import ocean_grid_generator as ogg
+
+PI_180 = ogg.PI_180
+Re = ogg._default_Re
+FIELDS = ("x", "y", "dx", "dy", "area", "angle_dx")
+
+
+class Piece(object):
+    """One sub-grid as it enters the stitch.  Vertex rows kept: [row0, rows_full)."""
+
+    def __init__(self, name, kind, rows_full, **params):
+        self.name, self.kind, self.rows_full, self.row0 = name, kind, int(rows_full), 0
+        self.p = params
+
+    @property
+    def rows(self):
+        return self.rows_full - self.row0
+
+    def cut(self, n):
+        self.row0 += int(n)
+
+
+class Plan(object):
+    def __init__(self, Ni, pieces, skip_metrics, info):
+        self.Ni, self.pieces, self.skip_metrics, self.info = int(Ni), pieces, bool(skip_metrics), info
+
+    @property
+    def nxp(self):
+        return self.Ni + 1
+
+    @property
+    def nyp(self):
+        return sum(p.rows - 1 for p in self.pieces) + 1
+
+    def offsets(self):
+        off, out = 0, []
+        for p in self.pieces:
+            out.append(off)
+            off += p.rows - 1
+        return out
+
+
+def _has(grids, name):
+    return name in grids or "all" in grids
+
+
+def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfracdp=None, south_cutoff_row=0,
+                   south_cutoff_ang=-90.0, enhanced_equatorial=0, grids="all", match_dy=(), skip_metrics=False,
+                   ensure_nj_even=False, shift_equator_to_u_point=True, bipolar_lower_lat=-99.0,
+                   mercator_lower_lat=-99.0, mercator_upper_lat=-99.0, south_ocean_lower_lat=-99.0,
+                   no_south_cap=False, **_unused):
+    """Sizing rules of OGG:969-1195 and the south cut of OGG:1270-1313, as data."""
+    doughnut = 0.28 * 7 / 4 if exfracdp is None else exfracdp                      # OGG:891-892
+    refineS, refineR, lenlon, lon0 = 2, inverse_resolution, 360, -300.0            # OGG:969-972
+    Ni = int(refineR * refineS * lenlon)                                           # OGG:974
+    phi_s_Merc, phi_n_Merc = -66.85954725, 64.05895973                             # OGG:987
+    if mercator_upper_lat > -90:
+        phi_n_Merc = mercator_upper_lat
+    if mercator_lower_lat > -90:
+        phi_s_Merc = mercator_lower_lat
+    if refineR == 2:
+        phi_s_Merc, phi_n_Merc = -68.0, 65.0                                       # OGG:996-998
+    if refineR == 1 and enhanced_equatorial:
+        phi_s_Merc, phi_n_Merc = -77.8, 60.0                                       # OGG:999-1001
+    info = {"lon0": lon0, "doughnut": doughnut}
+    lam1d = lon0 + numpy.arange(Ni + 1) * lenlon / float(Ni)                       # OGG:431, :834 (same law)
+
+    merc = bp = so = sc = None
+    if _has(grids, "mercator"):
+        phiM = ogg.mercator_latitudes(Ni, phi_s_Merc, phi_n_Merc, refineR, shift_equator_to_u_point, ensure_nj_even,
+                                      enhanced_equatorial)
+        if phiM.shape[0] % 2 == 0 and ensure_nj_even:                               # OGG:434-437
+            phiM = phiM[1:]
+        merc = Piece("Merc", "band", phiM.shape[0], lam=lam1d, phi=phiM)
+        DeltaPhiMerc_so = phiM[1] - phiM[0]                                         # OGG:1024-1025
+        DeltaPhiMerc_no = phiM[-1] - phiM[-2]
+        lat0_bp = phiM[-1]                                                          # OGG:1030
+        info["phiMerc"] = (phiM[0], phiM[-1])
+    if _has(grids, "bipolar"):
+        if bipolar_lower_lat > -90:
+            lat0_bp = bipolar_lower_lat
+        Nj_ncap = int(60 * refineR * refineS)                                       # OGG:1042
+        if refineR == 2:
+            Nj_ncap = 119 * refineS
+        if refineR == 1 and enhanced_equatorial:
+            Nj_ncap = 154
+        if "bp" in match_dy:
+            Nj_ncap = int(0.5 + (90.0 - lat0_bp) / DeltaPhiMerc_no)                 # OGG:1057
+        if Nj_ncap % 2 != 0 and ensure_nj_even:                                     # OGG:107-111
+            Nj_ncap -= 1
+        bp = Piece("BP", "bipolar", Nj_ncap + 1, Nj=Nj_ncap, lat0_bp=float(lat0_bp), lon_bp=lon0,
+                   rp=ogg.bipolar_rp(lat0_bp))
+    # Southern Ocean band (OGG:1080-1116)
+    lat0_SO = -78.0
+    if south_ocean_lower_lat > -90:
+        lat0_SO = south_ocean_lower_lat
+    if merc is None:
+        raise Exception("the Mercator sub-grid is required: the reference reads phiMerc at OGG:1083")
+    latUp_SO = merc.p["phi"][0]
+    lenlat_SO = latUp_SO - lat0_SO
+    deltaPhiSO = 1.0 / refineR / refineS
+    Nj_SO = int(refineR * 55)
+    if refineR == 2 and enhanced_equatorial:
+        Nj_SO = 109
+    if refineR == 1 and enhanced_equatorial:
+        Nj_SO = 0
+    if "so" in match_dy:
+        Nj_SO = int(0.5 + lenlat_SO / DeltaPhiMerc_so)                              # OGG:1097
+    info.update(latUp_SO=latUp_SO, lat0_SO=lat0_SO)
+    if Nj_SO != 0 and _has(grids, "so"):
+        lamSO, phiSO = ogg.latlon_vectors(Ni, Nj_SO, lon0, lenlon, lat0_SO, lenlat_SO, ensure_nj_even)
+        so = Piece("SO", "band", phiSO.shape[0], lam=lamSO, phi=phiSO)
+    if so is None:
+        raise Exception("the Southern Ocean sub-grid is required: the reference reads phiSO at OGG:1122")
+    # South cap (OGG:1122-1195)
+    lat0_SC = so.p["phi"][0]
+    if "p125sc" in match_dy:
+        lat0_SC = lat0_SO
+    Nj_scap = int(refineR * 40) * 7 // 4                                            # OGG:1127-1131
+    if no_south_cap or (refineR == 2 and enhanced_equatorial) or (refineR == 1 and enhanced_equatorial):
+        Nj_scap = 0
+    info["r_dp"] = r_dp
+    if Nj_scap != 0 and _has(grids, "sc"):
+        if r_dp == 0.0 and lat_dp <= -90.0:                                         # regular pole, OGG:1145-1157
+            fullArc = lat0_SC + 90.0
+            Nj_scap = int(fullArc / deltaPhiSO)
+            lamSC, phiSC = ogg.latlon_vectors(Ni, Nj_scap, lon0, lenlon, -90.0, 90 + lat0_SO, ensure_nj_even)
+            sc = Piece("SC", "band", phiSC.shape[0], lam=lamSC, phi=phiSC, regular=True)
+        else:                                                                       # displaced pole, OGG:1158-1195
+            if lat_dp > -90:
+                r_dp = float(np.tan((90 + lat_dp) * PI_180) / np.tan((90 + lat0_SC) * PI_180))   # OGG:1160
+                info["r_dp"] = r_dp
+            sc = Piece("SC", "dp", Nj_scap + 1, Ni=Ni, Nj=Nj_scap, lon0=lon0, lat0=float(lat0_SC), lon_dp=float(lon_dp),
+                       r_dp=float(r_dp))
+            if doughnut != 0.0:
+                jmin = numpy.ceil(doughnut * Nj_scap)                               # OGG:1178-1180
+                sc.cut(int(jmin + numpy.mod(jmin, 2)))
+            if sc.rows % 2 == 0 and ensure_nj_even:                                 # OGG:1188-1195
+                sc.cut(1)
+    info["lat0_SC"] = lat0_SC
+
+    # South cut (OGG:1270-1313)
+    cut, jcut = False, 0
+    if south_cutoff_row > 0:
+        cut, jcut = True, south_cutoff_row - 1
+    elif south_cutoff_ang > -90:
+        cut = True
+        jcut = 1 + numpy.nonzero(first_column_latitudes(sc) < south_cutoff_ang)[0][-1]
+    if cut:
+        if sc is not None and jcut < sc.rows:
+            if (sc.rows - jcut) % 2 == 0 and ensure_nj_even:
+                jcut += 1
+            print("   Cutting SC grid rows 0 to ", jcut)
+            sc.cut(jcut)
+        elif so is not None:
+            print("   Whole SC and some of SO need to be cut!")
+            jcut_SO = jcut - (sc.rows if sc is not None else 0)
+            sc = None
+            if ((so.rows - 1) - jcut_SO - 1) % 2 == 0 and ensure_nj_even:
+                jcut_SO += 1
+            print("   No SC grid remained. Cutting SO grid rows 0 to ", jcut_SO)
+            so.cut(jcut_SO)
+    pieces = [p for p in (sc, so, merc, bp) if p is not None]
+    info.update(hasSC=sc is not None, hasSO=so is not None, hasMerc=merc is not None, hasBP=bp is not None)
+    return Plan(Ni, pieces, skip_metrics, info)
+
+
+def first_column_latitudes(piece):
+    """phi[:, 0] of a piece's kept rows (needed by --south_cutoff_ang, OGG:1278)."""
+    if piece is None:
+        raise Exception("south_cutoff_ang needs the southern cap sub-grid (OGG:1278)")
+    if piece.kind == "band":
+        return piece.p["phi"][piece.row0:]
+    p = piece.p
+    _, phis, _, _ = ogg.displacedPoleCap_mesh(numpy.arange(1), numpy.arange(piece.row0, piece.rows_full), p["Ni"],
+                                              p["Nj"], p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"])
+    return phis[:, 0]
+
+
+# --------------------------------------------------------------------------------------------------
+# device build
+# --------------------------------------------------------------------------------------------------
+def slab_bounds(ncells, rank, world):
+    """Contiguous split of a piece's cell rows over `world` ranks (every rank gets a share of every piece)."""
+    base, rem = divmod(ncells, world)
+    c0 = rank * base + min(rank, rem)
+    return c0, c0 + base + (1 if rank < rem else 0)
+
+
+class Supergrid(object):
+    """The six arrays (device tensors) of one rank's share of the supergrid."""
+
+    def __init__(self, plan, rank=0, world=1):
+        self.plan, self.rank, self.world = plan, rank, world
+        self.slabs = [slab_bounds(p.rows - 1, rank, world) for p in plan.pieces]
+        self.rows_local = sum(c1 - c0 for c0, c1 in self.slabs)    # cell rows held here
+        nxp, nyl = plan.nxp, self.rows_local
+        self.x, self.y, self.angle_dx = _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp)
+        self.dx = _dev.empty(nyl + 1, nxp - 1)
+        self.dy, self.area = _dev.empty(nyl, nxp), _dev.empty(nyl, nxp - 1)
+        self._iv = None
+        self._lam_dev = {}
+
+    # number of vertex rows that are really this rank's (the closing row belongs to the last rank only)
+    @property
+    def vertex_rows(self):
+        return self.rows_local + (1 if self.rank == self.world - 1 else 0)
+
+    def arrays(self):
+        n = self.vertex_rows
+        return dict(x=self.x[:n], y=self.y[:n], dx=self.dx[:n], dy=self.dy, area=self.area, angle_dx=self.angle_dx[:n])
+
+    def build(self):
+        """Launch every piece's kernels on the current stream (asynchronous)."""
+        plan = self.plan
+        if plan.skip_metrics:                                       # OGG:1009-1011 etc.: metrics stay -1
+            self.dx.fill_(-1.0); self.dy.fill_(-1.0); self.area.fill_(-1.0)
+        off = 0
+        last = len(plan.pieces) - 1
+        for k, (piece, (c0, c1)) in enumerate(zip(plan.pieces, self.slabs)):
+            if c1 > c0:
+                closing = (k == last and self.rank == self.world - 1)
+                self._build_piece(piece, c0, c1, off, closing)
+            off += c1 - c0
+        return self
+
+    def _views(self, off, nrows_v):
+        nxp = self.plan.nxp
+        st = _dev.stream()
+        return (_dev.ptr_off(self.x, off * nxp), _dev.ptr_off(self.y, off * nxp), _dev.ptr_off(self.dx, off * (nxp - 1)),
+                _dev.ptr_off(self.dy, off * nxp), _dev.ptr_off(self.area, off * (nxp - 1)),
+                _dev.ptr_off(self.angle_dx, off * nxp), st)
+
+    def _build_piece(self, piece, c0, c1, off, closing):
+        plan, nxp = self.plan, self.plan.nxp
+        px, py, pdx, pdy, parea, pangle, st = self._views(off, c1 - c0 + 1)
+        if plan.skip_metrics:
+            pdx = pdy = parea = None
+        if piece.kind == "band":
+            key = id(piece)
+            if key not in self._lam_dev:
+                self._lam_dev[key] = (_dev.to_dev(piece.p["lam"]), _dev.to_dev(piece.p["phi"]))
+            lam, phi = self._lam_dev[key]
+            j0 = piece.row0 + c0
+            flags = 0 if closing else _cabi.OGG_BAND_SKIP_TOP_VERTEX_ROW
+            if plan.skip_metrics:
+                flags |= _cabi.OGG_BAND_NO_METRICS
+            _cabi.call("ogg_band_fill_metrics", _dev.ptr(lam), _dev.ptr_off(phi, j0), c1 - c0 + 1, nxp, Re, flags,
+                       px, py, pdx, pdy, parea, pangle, st)
+        elif piece.kind == "bipolar":
+            p = piece.p
+            j0, j1 = piece.row0 + c0, piece.row0 + c1
+            _cabi.call("ogg_bipolar_cap_mesh", plan.Ni, p["Nj"], j0, j1 + 1, p["lat0_bp"], p["lon_bp"], p["rp"],
+                       px, py, None, None, st)
+            _cabi.call("ogg_angle_x", px, py, c1 - c0 + 1, nxp, pangle, st)                       # OGG:1071
+            if not plan.skip_metrics:
+                _cabi.call("ogg_bipolar_cap_metrics_quad", 5, plan.Ni, p["Nj"], j0, j1, p["lat0_bp"], p["lon_bp"],
+                           p["rp"], Re, pdx, pdy, parea, st)                                       # OGG:1068
+                if j1 != p["Nj"]:
+                    self._dx_row_fix(piece, j1, off + (c1 - c0))
+        else:  # displaced pole
+            p = piece.p
+            j0, j1 = piece.row0 + c0, piece.row0 + c1
+            if self._iv is None:
+                self._iv = _dev.to_dev(numpy.arange(plan.Ni + 1))
+            jv = _dev.to_dev(numpy.arange(j0, j1 + 1))
+            _cabi.call("ogg_dp_mesh", _dev.ptr(self._iv), plan.Ni + 1, _dev.ptr(jv), j1 - j0 + 1, plan.Ni, p["Nj"],
+                       p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"], px, py, st)                   # OGG:1162
+            _cabi.call("ogg_angle_x", px, py, c1 - c0 + 1, nxp, pangle, st)                       # OGG:1163
+            if not plan.skip_metrics:
+                _cabi.call("ogg_dp_metrics_quad", 4, plan.Ni, p["Nj"], j0, j1, p["lon0"], p["lat0"], p["lon_dp"],
+                           p["r_dp"], Re, pdx, pdy, parea, st)                                     # OGG:1170
+
+    def _dx_row_fix(self, piece, j1, row):
+        """A slab that ends below the cap's top has no dx for its closing vertex row; it belongs to the next rank
+        (or is overwritten by the next piece), nothing to do."""
+        return
+
+    # ---- reductions / checks -------------------------------------------------------------------------
+    def area_sum(self):
+        return ogg.device_sum(self.area) if self.area.numel() else 0.0
+
+    def to_host(self):
+        return {k: _dev.to_host(v) for k, v in self.arrays().items()}
+
+
+def build_supergrid(plan, rank=0, world=1):
+    return Supergrid(plan, rank, world).build()
+
+
+def generate(**kwargs):
+    """Public one-call API: plan + build on this GPU; returns (plan, Supergrid) with arrays resident in HBM."""
+    _dev.ready()
+    plan = plan_supergrid(**kwargs)
+    return plan, build_supergrid(plan)
+
+
+# --------------------------------------------------------------------------------------------------
+# stand-alone sub-grids (for --write_subgrid_files and the CHECK_metrics lines)
+# --------------------------------------------------------------------------------------------------
+def build_piece_standalone(plan, piece):
+    sub = Plan(plan.Ni, [piece], plan.skip_metrics, plan.info)
+    return build_supergrid(sub)
+
+
+def _check_lines(plan, piece, sg):
+    a = sg.arrays()
+    if plan.skip_metrics:
+        return
+    if piece.kind == "band":
+        phi = piece.p["phi"][piece.row0:]
+        lat1, lat2 = phi[0], phi[-1]
+        if piece.p.get("regular"):
+            lat1, lat2 = phi[-1], phi[0]                                            # OGG:1157
+        label = "CHECK_metrics" if piece.name == "Merc" else "CHECK_metrics_MIDAS"
+        print("   %s: %% errors in (area, lat arc, lon arc)" % label,
+              ogg.metrics_error(a["dx"], a["dy"], a["area"], plan.Ni, lat1, lat2))
+    elif piece.kind == "bipolar":
+        print("   CHECK_metrics_hquad: % errors in (area, lat arc, lon arc1, lon arc2)",
+              ogg.metrics_error(a["dx"], a["dy"], a["area"], plan.Ni, piece.p["lat0_bp"], 90.0, bipolar=True))
+    else:
+        print("   CHECK_metrics_hquad: not evaluated (only the rows kept after the doughnut cut are generated)")
+
+
+def run_main(args):
+    """Body of main(**args) (OGG:855-1449)."""
+    _dev.ready()
+    match_dy, grids = args["match_dy"], args["grids"]
+    known_options = ["bp", "so", "p125sc", ""]
+    unknown = list(set(match_dy).difference(known_options))
+    if len(unknown) != 0:                                                           # OGG:883-888
+        print("Unknown options in match_dy: ", unknown)
+        print("Known options are one or more of ", known_options)
+        sys.exit(2)
+    if args["r_dp"] != 0.0 and args["lat_dp"] > -90.0:                              # OGG:904-907
+        print("Cannot specify both --rdp and --latdp for the displaced pole!")
+        ogg.usage()
+        sys.exit(2)
+    gridfilename, no_changing_meta, debug = args["gridfilename"], args["no_changing_meta"], args["debug"]
+    hist, desc, source = _metadata(args)
+    start_time = time.time()
+    plan_args = {k: v for k, v in args.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta",
+                                                             "write_subgrid_files", "reproduce_MIDAS_grids")}
+    plan = plan_supergrid(**plan_args)
+    info = plan.info
+    if args["write_subgrid_files"]:
+        for piece in plan.pieces:
+            sg = build_piece_standalone(plan, piece)
+            _check_lines(plan, piece, sg)
+            a = sg.arrays()
+            ogg.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], axis_units="degrees",
+                         fnam=gridfilename + piece.name + ".nc", description=desc, history=hist, source=source,
+                         debug=debug)
+    if len(plan.pieces) < 2:
+        raise Exception("nothing to stitch: the reference needs at least two adjoining sub-grids (OGG:1237-1247)")
+    print("Stitching the grids together...")
+    sg = build_supergrid(plan)
+    a = sg.arrays()
+    ycol = _dev.to_host(a["y"][:, plan.Ni // 4])
+    if info["hasBP"]:
+        dy3_ = numpy.roll(ycol, shift=-1, axis=0) - ycol                            # OGG:1366-1370
+        if numpy.any(dy3_ == 0):
+            raise Exception("lattitude array has repeated values along symmetry meridian!")
+    # description (OGG:1403-1423)
+    desc = desc + "It consists of; "
+    if info["hasMerc"]:
+        desc += "a Mercator grid spanning " + str(info["phiMerc"][0]) + " to " + str(info["phiMerc"][1]) + " degrees; "
+    if info["hasBP"]:
+        desc += "a bipolar northern cap north of " + str(info["phiMerc"][1]) + " degrees; "
+    if info["hasSO"]:
+        desc += "a regular lat-lon grid spanning " + str(info["latUp_SO"]) + " to " + str(info["lat0_SO"]) + " degrees; "
+    if info["hasSC"]:
+        desc += "a " + ("displaced pole " if info["r_dp"] != 0.0 else "regular ")
+        desc += "southern cap south of " + str(info["lat0_SO"]) + " degrees."
+    if args["south_cutoff_ang"] > -90:
+        desc += " It is cut south of " + str(args["south_cutoff_ang"]) + " degrees."
+    if args["south_cutoff_row"] > 0:
+        desc += " The first " + str(args["south_cutoff_row"]) + " rows at south are deleted."
+    equator_index = numpy.searchsorted(ycol, 0.0)                                   # OGG:1425-1436
+    if equator_index == 0:
+        raise Exception("   Ooops: Equator is not in the grid")
+    print("   Equator is at j=", equator_index)
+    if equator_index % 2 == 0:
+        raise Exception("Ooops: Equator is not going to be a u-point. Use option --south_cutoff_row to one more or on less row from south.")
+    if a["y"].shape[0] % 2 == 0:
+        raise Exception("Ooops: The number of j's in the supergrid is not even. Use option --south_cutoff_row to one more or on less row from south.")
+    print("shapes: ", tuple(a["x"].shape), tuple(a["y"].shape), tuple(a["dx"].shape), tuple(a["dy"].shape),
+          tuple(a["area"].shape), tuple(a["angle_dx"].shape))
+    ogg.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], axis_units="degrees", fnam=gridfilename,
+                 description=desc, history=hist, source=source, no_changing_meta=no_changing_meta, debug=debug)
+    print("Wrote the whole grid to file ", gridfilename)
+    print("runtime(secs)  %s" % (time.time() - start_time))
+    return sg
+
+
+def _metadata(args):
+    """history / description / source strings (OGG:909-963)."""
+    import datetime
+    import os
+    import socket
+    import subprocess
+    hist = "This grid file was generated via command " + " ".join(sys.argv)
+    desc = ("This is an orthogonal coordinate grid for the Earth with a nominal resoution of "
+            + str(1 / args["inverse_resolution"]) + " degrees along the equator. ")
+    source = ""
+    if not args["no_changing_meta"]:
+        hist += " on " + str(datetime.date.today()) + " on platform " + str(socket.gethostname())
+        here = os.path.dirname(os.path.abspath(__file__))
+        try:
+            githash = subprocess.check_output("cd " + here + ";git rev-parse HEAD; exit 0", stderr=subprocess.STDOUT,
+                                              shell=True).decode("ascii").rstrip("\n")
+        except Exception:
+            githash = "unknown"
+        source = (sys.argv[0] + " had git hash " + githash
+                  + ". B200-native build of the ocean_model_grid_generator supergrid path")
+    return hist, desc, source

@@ -1,0 +1,273 @@
+"""Parity tests proper: every C-ABI entry point (called through the drop-in Python mirror) against the CPU
+oracle on the same inputs and against the golden vectors produced by the unmodified reference.  Bar: bit-exact."""
+import numpy as np
+import pytest
+
+from util import assert_bits, sha
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def G():
+    from ocean_model_grid_generator_b200 import device, ocean_grid_generator
+    device.ready()
+    return ocean_grid_generator
+
+
+@pytest.fixture(scope="module")
+def dnp():
+    from ocean_model_grid_generator_b200 import devnp
+    return devnp
+
+
+UNARY = ["sin", "cos", "tan", "arcsin", "arccos", "arctan", "exp", "log", "sinh", "cosh"]
+
+
+@pytest.mark.parametrize("name", UNARY)
+def test_trig_device_equals_oracle(dnp, oracle, name):
+    rng = np.random.default_rng(17)
+    lo, hi = {"arcsin": (-1, 1), "arccos": (-1, 1), "log": (1e-6, 1e6), "exp": (-30, 30), "sinh": (-6, 6),
+              "cosh": (-6, 6), "tan": (-7, 7)}.get(name, (-400, 400))
+    x = np.concatenate([rng.uniform(lo, hi, 1000000), rng.uniform(lo, hi, 100000) * 1e-4,
+                        [0.0, -0.0, np.pi / 2, -np.pi / 2, 90 * (np.pi / 180), 0.4375, 0.6875, 1.1875, 2.4375, 1e-300]])
+    if name == "log":
+        x = np.abs(x) + 1e-300
+    if name in ("arcsin", "arccos"):
+        x = np.clip(x, -1, 1)
+        x[:6] = [0.0, 1.0, -1.0, 0.5, -0.5, -0.0]
+    assert_bits(getattr(dnp, name)(x), oracle.unary(name, x), name)
+
+
+def test_arctan2_and_mod(dnp, oracle):
+    rng = np.random.default_rng(18)
+    y, x = rng.uniform(-2, 2, 500000), rng.uniform(-2, 2, 500000)
+    y[:100] = 0.0; x[50:150] = 0.0; y[200:210] = -0.0
+    assert_bits(dnp.arctan2(y, x), oracle.arctan2(y, x), "arctan2")
+    a = np.concatenate([rng.uniform(-1000, 1000, 500000), [0.0, -0.0, 360.0, -360.0, 720.0, 359.99999999999994,
+                       -1e-20, 1e-20, 360.00000000000006, -359.99999999999994, 180.0, -180.0]])
+    assert_bits(dnp.mod360(a), oracle.mod360(a), "mod360")
+    assert_bits(dnp.mod360(a), np.mod(a, 360.0), "mod360 vs numpy")
+    assert float(dnp.tan(0.5)) == float(oracle.unary("tan", np.array([0.5]))[0])      # scalar path
+
+
+def test_trig_golden(dnp, golden):
+    t, u = golden["trig_arg"], golden["trig_uarg"]
+    for f in ("sin", "cos", "tan", "arctan", "sinh", "cosh", "exp"):
+        assert_bits(getattr(dnp, f)(t), golden["trig_" + f], f)
+    assert_bits(dnp.arcsin(u), golden["trig_arcsin"], "arcsin")
+    assert_bits(dnp.arccos(u), golden["trig_arccos"], "arccos")
+    assert_bits(dnp.log(np.abs(t) + 1e-3), golden["trig_log"], "log")
+    assert_bits(dnp.arctan2(t[:405], u), golden["trig_arctan2"], "arctan2")
+
+
+# ---- bipolar cap -----------------------------------------------------------------------------------
+def test_bipolar_golden(G, golden):
+    Ni, Nj, lat0, lon_bp, rp = golden["bp_params"]
+    Ni, Nj = int(Ni), int(Nj)
+    assert G.bipolar_rp(lat0) == rp
+    for g, k in zip(G.generate_bipolar_cap_mesh(Ni, Nj, lat0, lon_bp), ("bp_lams", "bp_phis", "bp_hi", "bp_hj")):
+        assert_bits(g, golden[k], k)
+    for order in (2, 3, 4, 5):
+        for g, k in zip(G.bipolar_cap_metrics_quad_fast(order, 12, 5, lat0, lon_bp, rp), ("dxq", "dyq", "daq")):
+            assert_bits(g, golden["bpq%d_%s" % (order, k)], "bpq%d %s" % (order, k))
+    for g, k in zip(G.bipolar_projection(golden["bpp_lamg"], golden["bpp_phig"], lon_bp, rp), ("lams", "phis", "hi", "hj")):
+        assert_bits(g, golden["bpp_" + k], "bipolar_projection " + k)
+    hi, hj = G.bipolar_projection(golden["bpp_lamg"], golden["bpp_phig"], lon_bp, rp, metrics_only=True)
+    assert_bits(hi, golden["bpp_hi"], "mo hi"); assert_bits(hj, golden["bpp_hj"], "mo hj")
+    hi, hj = G.bipolar_cap_ij_array(golden["bpij_i"], golden["bpij_j"], 12, 5, lat0, lon_bp, rp)
+    assert_bits(hi, golden["bpij_hi"], "ij hi"); assert_bits(hj, golden["bpij_hj"], "ij hj")
+
+
+@pytest.mark.parametrize("Ni,Nj,lat0", [(96, 20, 64.05895973), (360, 61, 65.0), (2880, 17, 60.0), (24, 3, 80.0)])
+def test_bipolar_vs_oracle(G, oracle, Ni, Nj, lat0):
+    lon_bp = -300.0
+    for g, r, n in zip(G.generate_bipolar_cap_mesh(Ni, Nj, lat0, lon_bp, ensure_nj_even=False),
+                       oracle.generate_bipolar_cap_mesh(Ni, Nj, lat0, lon_bp, ensure_nj_even=False), "lphj"):
+        assert_bits(g, r, "mesh " + n)
+    rp = G.bipolar_rp(lat0)
+    nyq = min(Nj, 9)
+    for order in (2, 3, 4, 5):
+        for g, r, n in zip(G.bipolar_cap_metrics_quad_fast(order, Ni // 4, nyq, lat0, lon_bp, rp),
+                           oracle.bipolar_cap_metrics_quad_fast(order, Ni // 4, nyq, lat0, lon_bp, rp), ("dxq", "dyq", "daq")):
+            assert_bits(g, r, "quad%d %s" % (order, n))
+    with pytest.raises(Exception, match="Uncoded order"):
+        G.bipolar_cap_metrics_quad_fast(6, 8, 4, lat0, lon_bp, rp)
+
+
+def test_bipolar_row_slabs_match_whole(G):
+    """Row-slab decomposition (what each GPU computes) reproduces the whole-cap result bit for bit."""
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    nx, ny, lat0, lon_bp = 64, 13, 64.05895973, -300.0
+    rp = G.bipolar_rp(lat0)
+    whole = G.bipolar_cap_metrics_quad_fast(5, nx, ny, lat0, lon_bp, rp)
+    for (j0, j1) in [(0, 5), (5, 6), (6, 13)]:
+        top = 1 if j1 == ny else 0
+        dxq, dyq, daq = D.empty(j1 - j0 + top, nx), D.empty(j1 - j0, nx + 1), D.empty(j1 - j0, nx)
+        _cabi.call("ogg_bipolar_cap_metrics_quad", 5, nx, ny, j0, j1, lat0, lon_bp, rp, 6371.0e3, D.ptr(dxq), D.ptr(dyq),
+                   D.ptr(daq), D.stream())
+        assert_bits(D.to_host(dxq), whole[0][j0:j1 + top], "dxq slab")
+        assert_bits(D.to_host(dyq), whole[1][j0:j1], "dyq slab")
+        assert_bits(D.to_host(daq), whole[2][j0:j1], "daq slab")
+
+
+# ---- displaced-pole cap ------------------------------------------------------------------------------
+def test_displaced_pole_golden(G, golden):
+    ni, nj, lon0, lat0, lon_dp, r_dp = golden["dp_params"]
+    ni, nj = int(ni), int(nj)
+    x, y, londp, latdp = G.generate_displaced_pole_grid(ni, nj, lon0, lat0, lon_dp, r_dp)
+    assert_bits(x, golden["dp_x"], "dp x"); assert_bits(y, golden["dp_y"], "dp y")
+    assert_bits(np.array([londp, latdp]), golden["dp_pole"], "pole")
+    for order in (2, 4):
+        for g, k in zip(G.displacedPoleCap_metrics_quad(order, 16, 6, lon0, lat0, lon_dp, r_dp), ("dxq", "dyq", "daq")):
+            assert_bits(g, golden["dpq%d_%s" % (order, k)], "dpq%d %s" % (order, k))
+    jj, ii = np.arange(0, 13) * 1.0, np.arange(0, 65) * 1.0
+    for order in (2, 4, 6):
+        assert_bits(G.numerical_hi(jj, ii, ni, nj, lon0, lat0, lon_dp, r_dp, 1e-3, order), golden["dp_hi%d" % order], "hi")
+        assert_bits(G.numerical_hj(jj, ii, ni, nj, lon0, lat0, lon_dp, r_dp, 1e-3, order), golden["dp_hj%d" % order], "hj")
+    assert_bits(G.great_arc_distance(jj, ii + 0.5, jj, ii - 0.25, ni, nj, lon0, lat0, lon_dp, r_dp), golden["dp_gad"], "gad")
+    rj, z0 = G.dp_constants(lat0, lon_dp, r_dp)
+    assert_bits(np.array([rj, z0.real, z0.imag]), golden["dp_consts"], "dp consts")
+    lam, phi = G.displacedPoleCap_projection(golden["dpp_lon"], golden["dpp_lat"], z0, rj)
+    assert_bits(lam, golden["dpp_lam"], "projection lam"); assert_bits(phi, golden["dpp_phi"], "projection phi")
+    assert_bits(G.monotonic_bounding(golden["mb_in"].copy(), -300.0), golden["mb_out"], "monotonic_bounding")
+    with pytest.raises(Exception, match="order not coded"):
+        G.displacedPoleCap_metrics_quad(5, 8, 4, lon0, lat0, lon_dp, r_dp)
+    with pytest.raises(Exception, match="Uncoded order"):
+        G.displacedPoleCap_metrics_quad(7, 8, 4, lon0, lat0, lon_dp, r_dp)
+    with pytest.raises(Exception, match="order not coded"):
+        G.numerical_hi(jj, ii, ni, nj, lon0, lat0, lon_dp, r_dp, 1e-3, 3)
+
+
+@pytest.mark.parametrize("ni,nj,lon_dp,r_dp", [(96, 14, 80.0, 0.2), (720, 35, 60.0, 0.35), (1440, 10, 80.0, 0.2),
+                                               (300, 7, -120.0, 0.05)])
+def test_displaced_pole_vs_oracle(G, oracle, ni, nj, lon_dp, r_dp):
+    lon0, lat0 = -300.0, -78.0
+    x, y, _, _ = G.generate_displaced_pole_grid(ni, nj, lon0, lat0, lon_dp, r_dp)
+    xo, yo, _, _ = oracle.generate_displaced_pole_grid(ni, nj, lon0, lat0, lon_dp, r_dp)
+    assert_bits(x, xo, "dp x"); assert_bits(y, yo, "dp y")
+    nxq, nyq = min(ni, 300), min(nj, 8)
+    for order in (2, 4):
+        for g, r, n in zip(G.displacedPoleCap_metrics_quad(order, nxq, nyq, lon0, lat0, lon_dp, r_dp),
+                           oracle.displacedPoleCap_metrics_quad(order, nxq, nyq, lon0, lat0, lon_dp, r_dp), ("dxq", "dyq", "daq")):
+            assert_bits(g, r, "dp quad%d %s" % (order, n))
+
+
+def test_monotonic_bounding_adversarial(G, oracle):
+    """Random jumps exercise every branch of the 2-state scan, including chains where the shift state flips often,
+    rows longer than one scan tile and values sitting on the 100-degree threshold."""
+    rng = np.random.default_rng(23)
+    for shape in [(3, 7), (5, 256), (4, 257), (6, 1000), (2, 5000)]:
+        x = rng.uniform(-200, 200, shape)
+        x[0, : min(shape[1], 6)] = [-300.0, -200.0, -100.0, 0.0, 100.0, 160.0][: min(shape[1], 6)]
+        x[1] = np.round(x[1] / 50.0) * 50.0              # many differences exactly 100, 150, ...
+        ref = oracle.monotonic_bounding(x.copy(), -300.0)
+        got = G.monotonic_bounding(x.copy(), -300.0)
+        assert_bits(got, ref, "monotonic %s" % (shape,))
+
+
+def test_dp_row_slabs_match_whole(G):
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    nx, ny = 120, 11
+    args = (-300.0, -78.0, 80.0, 0.2)
+    whole = G.displacedPoleCap_metrics_quad(4, nx, ny, *args)
+    for (j0, j1) in [(0, 4), (4, 5), (5, 11)]:
+        top = 1 if j1 == ny else 0
+        dxq, dyq, daq = D.empty(j1 - j0 + top, nx), D.empty(j1 - j0, nx + 1), D.empty(j1 - j0, nx)
+        _cabi.call("ogg_dp_metrics_quad", 4, nx, ny, j0, j1, *args, 6371.0e3, D.ptr(dxq), D.ptr(dyq), D.ptr(daq), D.stream())
+        assert_bits(D.to_host(dxq), whole[0][j0:j1 + top], "dxq slab")
+        assert_bits(D.to_host(dyq), whole[1][j0:j1], "dyq slab")
+        assert_bits(D.to_host(daq), whole[2][j0:j1], "daq slab")
+
+
+# ---- bands / spherical metrics ---------------------------------------------------------------------------
+def test_bands_golden(G, golden):
+    lam, phi = G.generate_latlon_grid(48, 9, -300., 360., -78., 11.3, ensure_nj_even=True)
+    assert_bits(lam, golden["ll_x"], "latlon x"); assert_bits(phi, golden["ll_y"], "latlon y")
+    meshes = {"ll": (golden["ll_x"], golden["ll_y"]), "bp": (golden["bp_lams"], golden["bp_phis"]),
+              "dp": (golden["dp_x"], golden["dp_y"])}
+    for nm, (mx, my) in meshes.items():
+        for fix in (True, False):
+            for g, k in zip(G.generate_grid_metrics_MIDAS(mx, my, latlon_areafix=fix), ("dx", "dy", "area")):
+                assert_bits(g, golden["midas_%s_%d_%s" % (nm, fix, k)], "midas %s %d %s" % (nm, fix, k))
+        assert_bits(G.angle_x(mx, my), golden["angle_" + nm], "angle " + nm)
+    with pytest.raises(Exception, match="same shape"):
+        G.angle_x(np.zeros((3, 4)), np.zeros((3, 5)))
+
+
+def test_mercator_golden(G, golden):
+    for r_, ps, pn, ee in [(0.25, -66.85954725, 64.05895973, 0), (1, -66.85954725, 64.05895973, 0), (2, -68.0, 65.0, 0),
+                           (2, -68.0, 65.0, 4), (1, -77.8, 60.0, 1), (4, -66.85954725, 64.05895973, 8)]:
+        Ni = int(r_ * 720)
+        x, y = G.generate_mercator_grid(Ni, ps, pn, -300., 360, r_, ensure_nj_even=False, enhanced_equatorial=ee)
+        assert_bits(y[:, 0], golden["merc_phi_r%s_e%d" % (r_, ee)], "mercator phi r=%s ee=%d" % (r_, ee))
+        assert (y == y[:, :1]).all() and x.shape == (y.shape[0], Ni + 1)
+        assert_bits(x[0], -300. + np.arange(Ni + 1) * 360 / float(Ni), "mercator lam")
+
+
+@pytest.mark.parametrize("shape", [(33, 130), (64, 129), (65, 31), (2, 2), (200, 1441)])
+def test_midas_general_vs_oracle(G, oracle, shape):
+    rng = np.random.default_rng(31)
+    nyp, nxp = shape
+    x = np.cumsum(rng.uniform(0, 360.0 / nxp * 2, shape), axis=1) - 300.0 + rng.normal(0, 0.01, shape)
+    y = np.cumsum(rng.uniform(0, 170.0 / nyp, shape), axis=0) - 85.0
+    for fix in (True, False):
+        if nyp < 2:
+            continue
+        for g, r, n in zip(G.generate_grid_metrics_MIDAS(x, y, latlon_areafix=fix),
+                           oracle.generate_grid_metrics_MIDAS(x, y, latlon_areafix=fix), ("dx", "dy", "area")):
+            assert_bits(g, r, "midas %s fix=%d %s" % (shape, fix, n))
+    assert_bits(G.angle_x(x, y), oracle.angle_x(x, y), "angle")
+
+
+def test_midas_halo_row_equals_whole(G, oracle):
+    """Row-slab MIDAS with the next slab's first row as halo == the whole-mesh result (the multi-GPU stencil)."""
+    rng = np.random.default_rng(37)
+    x = np.cumsum(rng.uniform(0, 1, (41, 77)), axis=1) - 300.0
+    y = np.cumsum(rng.uniform(0, 1, (41, 77)), axis=0) - 60.0
+    for fix in (True, False):
+        whole = oracle.generate_grid_metrics_MIDAS(x, y, latlon_areafix=fix)
+        for (a, b) in [(0, 17), (17, 18), (18, 41)]:
+            halo = (x[b], y[b]) if b < 41 else None
+            dx, dy, area = G.generate_grid_metrics_MIDAS(x[a:b], y[a:b], latlon_areafix=fix, halo=halo)
+            assert_bits(dx, whole[0][a:b], "dx"); nb = b if halo is not None else b - 1
+            assert_bits(dy, whole[1][a:nb], "dy"); assert_bits(area, whole[2][a:nb], "area")
+
+
+def test_band_fused_equals_general(G, oracle):
+    """The fused band kernel (tile + metrics + angle) against the general kernels and the oracle on the same band."""
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    lam = -300.0 + np.arange(1441) * 360 / 1440.0
+    phi = np.concatenate([[-90.0], np.sort(np.random.default_rng(3).uniform(-89.9, 89.9, 98)), [90.0]])
+    nyp, nxp = phi.size, lam.size
+    tl, tp = D.to_dev(lam), D.to_dev(phi)
+    o = [D.empty(nyp, nxp), D.empty(nyp, nxp), D.empty(nyp, nxp - 1), D.empty(nyp - 1, nxp), D.empty(nyp - 1, nxp - 1), D.empty(nyp, nxp)]
+    _cabi.call("ogg_band_fill_metrics", D.ptr(tl), D.ptr(tp), nyp, nxp, 6371.0e3, 0, *[D.ptr(t) for t in o], D.stream())
+    x, y = np.tile(lam, (nyp, 1)), np.tile(phi.reshape(-1, 1), (1, nxp))
+    assert_bits(D.to_host(o[0]), x, "x"); assert_bits(D.to_host(o[1]), y, "y")
+    dx, dy, area = oracle.generate_grid_metrics_MIDAS(x, y)
+    assert_bits(D.to_host(o[2]), dx, "dx"); assert_bits(D.to_host(o[3]), dy, "dy"); assert_bits(D.to_host(o[4]), area, "area")
+    assert_bits(D.to_host(o[5]), oracle.angle_x(x, y), "angle")
+
+
+def test_quad_helpers(G, oracle):
+    rng = np.random.default_rng(41)
+    for n in (2, 3, 4, 5):
+        a, b = G.quad_positions(n); ao, bo = oracle.quad_positions(n)
+        assert_bits(a, ao, "a"); assert_bits(b, bo, "b")
+        y = rng.uniform(size=n); y2 = rng.uniform(size=(n, n))
+        assert G.quad_average(y) == oracle.quad_average(y)
+        assert G.quad_average_2d(y2) == oracle.quad_average_2d(y2)
+    with pytest.raises(Exception, match="Uncoded order"):
+        G.quad_positions(6)
+    with pytest.raises(Exception, match="not squared"):
+        G.quad_average_2d(np.zeros((2, 3)))
+    with pytest.raises(Exception, match="Uncoded order"):
+        G.quad_average(np.zeros(6))
+
+
+def test_device_sum(G):
+    rng = np.random.default_rng(43)
+    a = rng.uniform(0, 1, (301, 77))
+    assert abs(G.device_sum(a) - a.sum()) <= 1e-12 * a.sum()
+    assert abs(G.device_sum(a, n=301, stride=77, offset=5) - a[:, 5].sum()) <= 1e-12 * a[:, 5].sum()
