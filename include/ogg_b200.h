@@ -121,6 +121,17 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
 /* out[0] = sum_{k<n} a[k*stride]   (fixed-shape tree: deterministic for given n) */
 int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, void* stream);
 
+/* ---- launch accounting (bench.py: gpu_launches and per-kernel CUDA-event durations) ---------------------------------- */
+/* kernels launched by this library since it was loaded */
+long long ogg_launch_count(void);
+/* when on, every launch is bracketed by CUDA events on its own stream */
+int ogg_timing_enable(int on);
+int ogg_timing_reset(void);
+int ogg_timing_kernels(void);          /* number of kernel classes */
+const char* ogg_timing_name(int id);   /* class name, e.g. "dp_hsamples" */
+/* total milliseconds and launch count of class `id` since the last reset (synchronises on the recorded events) */
+int ogg_timing_get(int id, double* ms_total, long long* launches);
+
 /* ---- measurement aid: FP64 add/mul issue rate (no FMA), the cap kernels' roofline denominator ------------------------ */
 /* runs iters dependent DADD/DMUL pairs x 8 independent chains per thread on every SM; returns via *gops_host the
  * achieved 1e9 instructions/s.  Synchronous. */

@@ -44,6 +44,8 @@ SIGNATURES = {
     "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _dp, _dp, _dp, _vp],
     "ogg_sum_strided": [_dp, _i64, _i64, _dp, _vp],
     "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
+    "ogg_launch_count": [], "ogg_timing_enable": [_int], "ogg_timing_reset": [], "ogg_timing_kernels": [],
+    "ogg_timing_name": [_int], "ogg_timing_get": [_int, ctypes.POINTER(_d), ctypes.POINTER(ctypes.c_longlong)],
     "ogg_device_count": [],
     "ogg_version": [],
 }
@@ -77,7 +79,8 @@ def load(build_if_missing=True):
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.argtypes = argtypes
-        fn.restype = ctypes.c_char_p if name == "ogg_version" else _int
+        fn.restype = (ctypes.c_char_p if name in ("ogg_version", "ogg_timing_name")
+                      else ctypes.c_longlong if name == "ogg_launch_count" else _int)
     _LIB = lib
     return lib
 

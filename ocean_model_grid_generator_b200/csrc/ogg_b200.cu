@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <vector>
 
 #include "../../include/ogg_b200.h"
 #include "ogg_trig.cuh"
@@ -59,6 +60,54 @@ struct Scratch {
   }
 };
 
+
+// ------------------------------------------------------------------------------------------------
+// launch accounting: every kernel launch goes through OGG_LAUNCH -- counted, and (when enabled by
+// ogg_timing_enable) bracketed by CUDA events on the launching stream so that bench.py can report each
+// kernel's own duration inside the timed region.
+// ------------------------------------------------------------------------------------------------
+enum KernelId { KID_ELEMENTWISE, KID_BAND_TABLES, KID_BAND_FILL, KID_MIDAS, KID_ANGLE, KID_BP_PROJECTION, KID_BP_TABLES,
+                KID_BP_MESH, KID_BP_SAMPLES, KID_SAMPLE_INDEX, KID_QUAD, KID_DP_SETUP, KID_DP_TABLES, KID_DP_RAW,
+                KID_MONOTONIC, KID_DP_HSAMPLES, KID_REDUCE, KID_COUNT };
+static const char* const kKernelNames[KID_COUNT] = {
+    "elementwise", "band_tables", "band_fill", "midas", "angle_x", "bipolar_projection", "bipolar_tables", "bipolar_mesh",
+    "bipolar_samples", "sample_index", "quad_cells", "dp_setup", "dp_tables", "dp_raw", "monotonic_bounding", "dp_hsamples",
+    "reduce"};
+static long long g_launches = 0;
+static bool g_timing = false;
+struct TimedLaunch { int id; cudaEvent_t e0, e1; };
+static std::vector<TimedLaunch> g_timed;
+static std::vector<cudaEvent_t> g_event_pool;
+static cudaEvent_t take_event() {
+  if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+static inline void launch_begin(int id, cudaStream_t st) {
+  ++g_launches;
+  if (g_timing) {
+    TimedLaunch t{id, take_event(), take_event()};
+    cudaEventRecord(t.e0, st);
+    g_timed.push_back(t);
+  }
+}
+static inline void launch_end(cudaStream_t st) {
+  if (g_timing) cudaEventRecord(g_timed.back().e1, st);
+}
+template <typename K, typename... A>
+static inline void launch_cfg(cudaStream_t st, dim3 g, dim3 b, K k, A... a) {
+  k<<<g, b, 0, st>>>(a...);
+}
+#define OGG_UNPAREN(...) __VA_ARGS__
+#define OGG_LAUNCH(ID, KERNEL, GRID_BLOCK, STREAM, ...)                              \
+  do {                                                                               \
+    cudaStream_t st__ = OGG_UNPAREN STREAM;                                          \
+    launch_begin(ID, st__);                                                          \
+    launch_cfg(st__, OGG_UNPAREN GRID_BLOCK, OGG_UNPAREN KERNEL, __VA_ARGS__);       \
+    launch_end(st__);                                                                \
+  } while (0)
+
 // ------------------------------------------------------------------------------------------------
 // element-wise portable functions
 // ------------------------------------------------------------------------------------------------
@@ -100,7 +149,7 @@ template <int F>
 static int launch_unary(const double* in, double* out, i64 n, void* stream) {
   if (n < 0 || (n > 0 && (!in || !out))) return OGG_ERR_ARG;
   if (n == 0) return OGG_OK;
-  k_unary<F><<<flat_grid(n), 256, 0, S(stream)>>>(in, out, n);
+  OGG_LAUNCH(KID_ELEMENTWISE, (k_unary<F>), (flat_grid(n), 256), (S(stream)), in, out, n);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -881,10 +930,10 @@ static dim3 lattice_grid(i64 ncol, i64 nrow, int threads) {
 
 template <typename KERN, typename... Args>
 static int launch_quad(int order, KERN k2, KERN k3, KERN k4, KERN k5, dim3 g, dim3 b, cudaStream_t st, Args... args) {
-  if (order == 2) k2<<<g, b, 0, st>>>(args...);
-  else if (order == 3) k3<<<g, b, 0, st>>>(args...);
-  else if (order == 4) k4<<<g, b, 0, st>>>(args...);
-  else k5<<<g, b, 0, st>>>(args...);
+  if (order == 2) OGG_LAUNCH(KID_QUAD, (k2), (g, b), (st), args...);
+  else if (order == 3) OGG_LAUNCH(KID_QUAD, (k3), (g, b), (st), args...);
+  else if (order == 4) OGG_LAUNCH(KID_QUAD, (k4), (g, b), (st), args...);
+  else OGG_LAUNCH(KID_QUAD, (k5), (g, b), (st), args...);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -919,6 +968,35 @@ int ogg_device_count(void) {
   return n;
 }
 
+long long ogg_launch_count(void) { return g_launches; }
+int ogg_timing_enable(int on) {
+  g_timing = on != 0;
+  return OGG_OK;
+}
+int ogg_timing_reset(void) {
+  for (auto& t : g_timed) { g_event_pool.push_back(t.e0); g_event_pool.push_back(t.e1); }
+  g_timed.clear();
+  return OGG_OK;
+}
+int ogg_timing_kernels(void) { return KID_COUNT; }
+const char* ogg_timing_name(int id) { return (id >= 0 && id < KID_COUNT) ? kKernelNames[id] : ""; }
+int ogg_timing_get(int id, double* ms_total, long long* launches) {
+  if (id < 0 || id >= KID_COUNT || !ms_total || !launches) return OGG_ERR_ARG;
+  double tot = 0.0;
+  long long n = 0;
+  for (auto& t : g_timed) {
+    if (t.id != id) continue;
+    OGG_CUDA(cudaEventSynchronize(t.e1));
+    float ms = 0.f;
+    OGG_CUDA(cudaEventElapsedTime(&ms, t.e0, t.e1));
+    tot += ms;
+    ++n;
+  }
+  *ms_total = tot;
+  *launches = n;
+  return OGG_OK;
+}
+
 int ogg_sin(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_SIN>(in, out, n, s); }
 int ogg_cos(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_COS>(in, out, n, s); }
 int ogg_tan(const double* in, double* out, int64_t n, void* s) { return launch_unary<F_TAN>(in, out, n, s); }
@@ -933,7 +1011,7 @@ int ogg_mod360(const double* in, double* out, int64_t n, void* s) { return launc
 int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* stream) {
   if (n < 0 || (n > 0 && (!y || !x || !out))) return OGG_ERR_ARG;
   if (n == 0) return OGG_OK;
-  k_atan2<<<flat_grid(n), 256, 0, S(stream)>>>(y, x, out, n);
+  OGG_LAUNCH(KID_ELEMENTWISE, (k_atan2), (flat_grid(n), 256), (S(stream)), y, x, out, n);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -947,12 +1025,12 @@ int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int
   OGG_CUDA(ws.get(&dxi, nxp)); OGG_CUDA(ws.get(&hx, nxp)); OGG_CUDA(ws.get(&xd, nxp));
   OGG_CUDA(ws.get(&cl, nyp)); OGG_CUDA(ws.get(&cy, nyp)); OGG_CUDA(ws.get(&dyr, nyp)); OGG_CUDA(ws.get(&dsl, nyp));
   const i64 m = nxp > nyp ? nxp : nyp;
-  k_band_tables<<<cdiv_u(m, 256), 256, 0, st>>>(lam, phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
+  OGG_LAUNCH(KID_BAND_TABLES, (k_band_tables), (cdiv_u(m, 256), 256), (st), lam, phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
   OGG_LAUNCH_CHECK();
   const i64 nyp_v = (flags & OGG_BAND_SKIP_TOP_VERTEX_ROW) ? nyp - 1 : nyp;
   const int metrics = (flags & OGG_BAND_NO_METRICS) ? 0 : 1;
   dim3 g(cdiv_u(nxp, 256), cdiv_u(nyp, kBandRows));
-  k_band_fill<<<g, 256, 0, st>>>(lam, phi, dxi, hx, xd, cl, cy, dyr, dsl, nyp, nxp, nyp_v, Re, Re * Re, metrics, x, y, dx,
+  OGG_LAUNCH(KID_BAND_FILL, (k_band_fill), (g, 256), (st), lam, phi, dxi, hx, xd, cl, cy, dyr, dsl, nyp, nxp, nyp_v, Re, Re * Re, metrics, x, y, dx,
                                  dy, area, angle);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
@@ -965,7 +1043,7 @@ int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp
   cudaStream_t st = S(stream);
   const i64 nrows = nyp + (halo_x ? 1 : 0);
   dim3 g(cdiv_u(nxp, 128), cdiv_u(nrows, kMidasRows));
-  k_midas<<<g, 128, 0, st>>>(x, y, nyp, nxp, Re, Re * Re, areafix, halo_x, halo_y, dx, dy, area);
+  OGG_LAUNCH(KID_MIDAS, (k_midas), (g, 128), (st), x, y, nyp, nxp, Re, Re * Re, areafix, halo_x, halo_y, dx, dy, area);
   OGG_LAUNCH_CHECK();
   if (!areafix && area) {
     if (!dx || !dy) return OGG_ERR_ARG;
@@ -975,10 +1053,10 @@ int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp
       double* top = nullptr;
       if (halo_x) {
         OGG_CUDA(ws.get(&top, nx));
-        k_dx_row<<<cdiv_u(nx, 256), 256, 0, st>>>(halo_x, halo_y, nx, Re, top);
+        OGG_LAUNCH(KID_MIDAS, (k_dx_row), (cdiv_u(nx, 256), 256), (st), halo_x, halo_y, nx, Re, top);
         OGG_LAUNCH_CHECK();
       }
-      k_area_nofix<<<flat_grid(ny * nx), 256, 0, st>>>(dx, top, dy, ny, nx, area);
+      OGG_LAUNCH(KID_MIDAS, (k_area_nofix), (flat_grid(ny * nx), 256), (st), dx, top, dy, ny, nx, area);
       OGG_LAUNCH_CHECK();
     }
   }
@@ -987,7 +1065,7 @@ int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp
 
 int ogg_angle_x(const double* x, const double* y, int64_t nyp, int64_t nxp, double* angle, void* stream) {
   if (!x || !y || !angle || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
-  k_angle<<<lattice_grid(nxp, nyp, 256), 256, 0, S(stream)>>>(x, y, nyp, nxp, angle);
+  OGG_LAUNCH(KID_ANGLE, (k_angle), (lattice_grid(nxp, nyp, 256), 256), (S(stream)), x, y, nyp, nxp, angle);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -997,7 +1075,7 @@ int ogg_bipolar_projection(const double* lamg, const double* phig, int64_t n, do
   if (n < 0 || (n > 0 && (!lamg || !phig))) return OGG_ERR_ARG;
   if (!metrics_only && (!lams || !phis)) return OGG_ERR_ARG;
   if (n == 0) return OGG_OK;
-  k_bp_projection<<<flat_grid(n), 256, 0, S(stream)>>>(lamg, phig, n, lon_bp, rp, metrics_only, lams, phis, hi, hj);
+  OGG_LAUNCH(KID_BP_PROJECTION, (k_bp_projection), (flat_grid(n), 256), (S(stream)), lamg, phig, n, lon_bp, rp, metrics_only, lams, phis, hi, hj);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1011,9 +1089,9 @@ int ogg_bipolar_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double 
   BpCol* ct; BpRow* rt;
   OGG_CUDA(ws.get(&ct, ncol)); OGG_CUDA(ws.get(&rt, nrow));
   const i64 m = ncol > nrow ? ncol : nrow;
-  k_bp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(nullptr, 0, ncol, nullptr, j0, nrow, Ni, Nj, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(m, 256), 256), (st), nullptr, 0, ncol, nullptr, j0, nrow, Ni, Nj, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
-  k_bp_lattice<0><<<lattice_grid(ncol, nrow, 256), 256, 0, st>>>(ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
+  OGG_LAUNCH(KID_BP_MESH, (k_bp_lattice<0>), (lattice_grid(ncol, nrow, 256), 256), (st), ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
                                                                  phis, h_i_inv, h_j_inv);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
@@ -1027,9 +1105,9 @@ int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64
   BpCol* ct; BpRow* rt;
   OGG_CUDA(ws.get(&ct, ni)); OGG_CUDA(ws.get(&rt, nj));
   const i64 m = ni > nj ? ni : nj;
-  k_bp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(i, 0, ni, j, 0, nj, Ni, Nj_ncap, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(m, 256), 256), (st), i, 0, ni, j, 0, nj, Ni, Nj_ncap, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
-  k_bp_lattice<1><<<lattice_grid(ni, nj, 256), 256, 0, st>>>(ct, rt, nj, ni, Ni, Nj_ncap, 0, lat0_bp, lon_bp, rp, h_i_inv,
+  OGG_LAUNCH(KID_BP_SAMPLES, (k_bp_lattice<1>), (lattice_grid(ni, nj, 256), 256), (st), ct, rt, nj, ni, Ni, Nj_ncap, 0, lat0_bp, lon_bp, rp, h_i_inv,
                                                              h_j_inv, nullptr, nullptr);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
@@ -1052,19 +1130,19 @@ int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, 
   OGG_CUDA(ws.get(&iv, nuc)); OGG_CUDA(ws.get(&jv, max_nur));
   OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, max_nur));
   OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
-  k_sample_index<<<cdiv_u(nuc + 1, 256), 256, 0, st>>>(q, order, 0, nx, nx, 0, iv);
+  OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nuc + 1, 256), 256), (st), q, order, 0, nx, nx, 0, iv);
   OGG_LAUNCH_CHECK();
-  k_bp_tables<<<cdiv_u(nuc, 256), 256, 0, st>>>(iv, 0, nuc, nullptr, 0, 0, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(nuc, 256), 256), (st), iv, 0, nuc, nullptr, 0, 0, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
   for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
     const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
     const bool top = c1 == ny;
     const i64 nur = (order - 1) * (c1 - c0) + 1 + (top ? 1 : 0);
-    k_sample_index<<<cdiv_u(nur + 1, 256), 256, 0, st>>>(q, order, c0, c1, ny, 1, jv);   // :144-151
+    OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nur + 1, 256), 256), (st), q, order, c0, c1, ny, 1, jv);   // :144-151
     OGG_LAUNCH_CHECK();
-    k_bp_tables<<<cdiv_u(nur, 256), 256, 0, st>>>(nullptr, 0, 0, jv, 0, nur, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
+    OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(nur, 256), 256), (st), nullptr, 0, 0, jv, 0, nur, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
     OGG_LAUNCH_CHECK();
-    k_bp_lattice<1><<<lattice_grid(nuc, nur, 256), 256, 0, st>>>(ct, rt, nur, nuc, nx, ny, 0, lat0_bp, lon_bp, rp, sx, sy,
+    OGG_LAUNCH(KID_BP_SAMPLES, (k_bp_lattice<1>), (lattice_grid(nuc, nur, 256), 256), (st), ct, rt, nur, nuc, nx, ny, 0, lat0_bp, lon_bp, rp, sx, sy,
                                                                  nullptr, nullptr);
     OGG_LAUNCH_CHECK();
     int rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
@@ -1095,7 +1173,7 @@ int ogg_quad_average_2d(const double* y, int64_t m, int n, double* out, void* st
 
 int ogg_dp_constants(double lat0, double lam_pole, double r_pole, double* out3, void* stream) {
   if (!out3) return OGG_ERR_ARG;
-  k_dp_constants<<<1, 32, 0, S(stream)>>>(lat0, lam_pole, r_pole, out3);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (S(stream)), lat0, lam_pole, r_pole, out3);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1103,7 +1181,7 @@ int ogg_dp_constants(double lat0, double lam_pole, double r_pole, double* out3, 
 int ogg_monotonic_bounding(double* x, int64_t nj, int64_t ni, double x_0, void* stream) {
   if (!x || nj < 1 || ni < 1) return OGG_ERR_ARG;
   const i64 cap = (i64)num_sms() * 8;
-  k_monotonic<<<(unsigned)(nj < cap ? nj : cap), kScanThreads, 0, S(stream)>>>(x, nj, ni, x_0, nullptr);
+  OGG_LAUNCH(KID_MONOTONIC, (k_monotonic), ((unsigned)(nj < cap ? nj : cap), kScanThreads), (S(stream)), x, nj, ni, x_0, nullptr);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1115,12 +1193,12 @@ int ogg_dp_projection(const double* lon, const double* lat, int64_t nj, int64_t 
   Scratch ws(st);
   double* cst;
   OGG_CUDA(ws.get(&cst, 3));
-  k_set3<<<1, 32, 0, st>>>(r_joint, z0_re, z0_im, cst);
+  OGG_LAUNCH(KID_DP_SETUP, (k_set3), (1, 32), (st), r_joint, z0_re, z0_im, cst);
   OGG_LAUNCH_CHECK();
-  k_dp_projection_raw<<<flat_grid(nj * ni), 256, 0, st>>>(lon, lat, nj * ni, cst, lam, phi);
+  OGG_LAUNCH(KID_DP_RAW, (k_dp_projection_raw), (flat_grid(nj * ni), 256), (st), lon, lat, nj * ni, cst, lam, phi);
   OGG_LAUNCH_CHECK();
   const i64 cap = (i64)num_sms() * 8;
-  k_monotonic<<<(unsigned)(nj < cap ? nj : cap), kScanThreads, 0, st>>>(lam, nj, ni, 0.0, lon);  // x_0 = lon_grid[0,0] (:463)
+  OGG_LAUNCH(KID_MONOTONIC, (k_monotonic), ((unsigned)(nj < cap ? nj : cap), kScanThreads), (st), lam, nj, ni, 0.0, lon);  // x_0 = lon_grid[0,0] (:463)
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1135,15 +1213,15 @@ static int dp_mesh_dev(const double* iv, i64 nil, double ishift, const double* j
   Cx* ct; double* rt; double* x0;
   OGG_CUDA(ws.get(&ct, nil)); OGG_CUDA(ws.get(&rt, njl)); OGG_CUDA(ws.get(&x0, 12));
   const i64 m = nil > njl ? nil : njl;
-  k_dp_tables<<<cdiv_u(m, 256), 256, 0, st>>>(iv, nil, ishift, jv, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
+  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables), (cdiv_u(m, 256), 256), (st), iv, nil, ishift, jv, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
   OGG_LAUNCH_CHECK();
-  k_dp_lattice_raw<<<lattice_grid(nil, njl, 256), 256, 0, st>>>(ct, rt, njl, nil, cst, lams, phis);
+  OGG_LAUNCH(KID_DP_RAW, (k_dp_lattice_raw), (lattice_grid(nil, njl, 256), 256), (st), ct, rt, njl, nil, cst, lams, phis);
   OGG_LAUNCH_CHECK();
   // x_0 = lon_grid[0,0] = lon0 + ((i[0]+shift)*360)/ni : reuse k_dp_x0<1> slots (kind 0 = plus shift, kind 2 = none)
-  k_dp_x0<1><<<1, 32, 0, st>>>(iv, ishift, ni, lon0, x0);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, ishift, ni, lon0, x0);
   OGG_LAUNCH_CHECK();
   const i64 cap = (i64)num_sms() * 8;
-  k_monotonic<<<(unsigned)(njl < cap ? njl : cap), kScanThreads, 0, st>>>(lams, njl, nil, 0.0, ishift != 0.0 ? x0 + 0 : x0 + 2);
+  OGG_LAUNCH(KID_MONOTONIC, (k_monotonic), ((unsigned)(njl < cap ? njl : cap), kScanThreads), (st), lams, njl, nil, 0.0, ishift != 0.0 ? x0 + 0 : x0 + 2);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1158,7 +1236,7 @@ int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int6
   Scratch ws(st);
   double* cst;
   OGG_CUDA(ws.get(&cst, 3));
-  k_dp_constants<<<1, 32, 0, st>>>(lat0, lam_pole, r_pole, cst);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lam_pole, r_pole, cst);
   OGG_LAUNCH_CHECK();
   return dp_mesh_dev(i, nil, 0.0, j, njl, 0.0, ni, nj, lon0, lat0, cst, lams, phis, st);
 }
@@ -1173,13 +1251,13 @@ int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1,
   double *cst, *l0, *p0, *l1, *p1;
   OGG_CUDA(ws.get(&cst, 3));
   OGG_CUDA(ws.get(&l0, n)); OGG_CUDA(ws.get(&p0, n)); OGG_CUDA(ws.get(&l1, n)); OGG_CUDA(ws.get(&p1, n));
-  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lon_dp, r_dp, cst);
   OGG_LAUNCH_CHECK();
   int rc = dp_mesh_dev(i0, nil, 0.0, j0, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
   if (rc) return rc;
   rc = dp_mesh_dev(i1, nil, 0.0, j1, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
   if (rc) return rc;
-  k_haversine<<<flat_grid(n), 256, 0, st>>>(l0, p0, l1, p1, n, out);
+  OGG_LAUNCH(KID_ELEMENTWISE, (k_haversine), (flat_grid(n), 256), (st), l0, p0, l1, p1, n, out);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1214,7 +1292,7 @@ static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow,
                          const double* cst, int nv, double eps, Cx* ct, double* rt, cudaStream_t st) {
   const i64 m = (ct ? ncol : 0) > (rt ? nrow : 0) ? (ct ? ncol : 0) : (rt ? nrow : 0);
   if (m == 0) return OGG_OK;
-  k_dp_tables_multi<<<cdiv_u(m, 256), 256, 0, st>>>(iv, ncol, jv, nrow, ni, nj, lon0, lat0, cst, nv, eps, ct, rt);
+  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables_multi), (cdiv_u(m, 256), 256), (st), iv, ncol, jv, nrow, ni, nj, lon0, lat0, cst, nv, eps, ct, rt);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1222,16 +1300,16 @@ static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 nco
                        double reps, double* hx, double* hy, cudaStream_t st) {
   const i64 cap = (i64)num_sms() * 4;
   const unsigned g = (unsigned)(nrow < cap ? nrow : cap);
-  if (nv == 1) k_dp_hsamples<1><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
-  else if (nv == 2) k_dp_hsamples<2><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
-  else k_dp_hsamples<3><<<g, kScanThreads, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  if (nv == 1) OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<1>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  else if (nv == 2) OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<2>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
+  else OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<3>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
 static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
-  if (nv == 1) k_dp_x0<1><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
-  else if (nv == 2) k_dp_x0<2><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
-  else k_dp_x0<3><<<1, 32, 0, st>>>(iv, eps, ni, lon0, x0v);
+  if (nv == 1) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, eps, ni, lon0, x0v);
+  else if (nv == 2) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<2>), (1, 32), (st), iv, eps, ni, lon0, x0v);
+  else OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<3>), (1, 32), (st), iv, eps, ni, lon0, x0v);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1252,7 +1330,7 @@ int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i
   OGG_CUDA(ws.get(&cst, 3));
   OGG_CUDA(ws.get(&l0, n)); OGG_CUDA(ws.get(&p0, n)); OGG_CUDA(ws.get(&l1, n)); OGG_CUDA(ws.get(&p1, n));
   for (int m = 0; m < nds; ++m) OGG_CUDA(ws.get(&ds[m], n));
-  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lon_dp, r_dp, cst);
   OGG_LAUNCH_CHECK();
   for (int m = 0; m < nds; ++m) {
     const double s = m == 0 ? eps : (m == 1 ? 2.0 * eps : 3.0 * eps);
@@ -1265,10 +1343,10 @@ int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i
       if (!rc) rc = dp_mesh_dev(i, nil, 0.0, j, njl, -s, nx, ny, lon0, lat0, cst, l1, p1, st);
     }
     if (rc) return rc;
-    k_haversine<<<flat_grid(n), 256, 0, st>>>(l0, p0, l1, p1, n, ds[m]);
+    OGG_LAUNCH(KID_ELEMENTWISE, (k_haversine), (flat_grid(n), 256), (st), l0, p0, l1, p1, n, ds[m]);
     OGG_LAUNCH_CHECK();
   }
-  k_fd_combine<<<flat_grid(n), 256, 0, st>>>(ds[0], ds[1], ds[2], order, 1.0 / eps, n, out);
+  OGG_LAUNCH(KID_ELEMENTWISE, (k_fd_combine), (flat_grid(n), 256), (st), ds[0], ds[1], ds[2], order, 1.0 / eps, n, out);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1293,9 +1371,9 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
   OGG_CUDA(ws.get(&cst, 3)); OGG_CUDA(ws.get(&iv, nuc + 1)); OGG_CUDA(ws.get(&jv, max_nur));
   OGG_CUDA(ws.get(&ct, nuc * nt)); OGG_CUDA(ws.get(&rt, max_nur * nt)); OGG_CUDA(ws.get(&x0v, 12));
   OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
-  k_dp_constants<<<1, 32, 0, st>>>(lat0, lon_dp, r_dp, cst);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lon_dp, r_dp, cst);
   OGG_LAUNCH_CHECK();
-  k_sample_index<<<cdiv_u(nuc + 1, 256), 256, 0, st>>>(q, order, 0, nx, nx, 0, iv);       // :578-581
+  OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nuc + 1, 256), 256), (st), q, order, 0, nx, nx, 0, iv);       // :578-581
   OGG_LAUNCH_CHECK();
   int rc = dp_tables_for(iv, nuc, nullptr, 0, nx, ny, lon0, lat0, cst, nv, eps, ct, nullptr, st);
   if (rc) return rc;
@@ -1305,7 +1383,7 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
     const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
     const bool top = c1 == ny;
     const i64 nur = (order - 1) * (c1 - c0) + 1;                                           // closing row = row ny when top
-    k_sample_index<<<cdiv_u(nur + 1, 256), 256, 0, st>>>(q, order, c0, c1, ny, 0, jv);    // :573-576
+    OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nur + 1, 256), 256), (st), q, order, c0, c1, ny, 0, jv);    // :573-576
     OGG_LAUNCH_CHECK();
     rc = dp_tables_for(nullptr, 0, jv, nur, nx, ny, lon0, lat0, cst, nv, eps, nullptr, rt, st);
     if (rc) return rc;
@@ -1324,9 +1402,9 @@ int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, voi
   Scratch ws(st);
   double* partial;
   OGG_CUDA(ws.get(&partial, kRedBlocks));
-  k_sum_partial<<<kRedBlocks, kRedThreads, 0, st>>>(a, n, stride, partial);
+  OGG_LAUNCH(KID_REDUCE, (k_sum_partial), (kRedBlocks, kRedThreads), (st), a, n, stride, partial);
   OGG_LAUNCH_CHECK();
-  k_sum_final<<<1, kRedThreads, 0, st>>>(partial, kRedBlocks, out);
+  OGG_LAUNCH(KID_REDUCE, (k_sum_final), (1, kRedThreads), (st), partial, kRedBlocks, out);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }

@@ -39,7 +39,7 @@ CONFIGS = {  # extras/Makefile:28-39 (file name / subgrid flags dropped; they do
     "res0.25_om5proto": "-r 4 --south_ocean_lower_lat -88.57 --match_dy so --no_south_cap --no_changing_meta",
     # BASELINE.json configs[0] geometry through the CLI that exists in this snapshot
     "readme_dp": "-r 2 --lon_dp 60.0 --lat_dp -85.85 --no_changing_meta",
-    "res1.0_dp": "-r 1.0 --r_dp 0.2 --no_changing_meta",
+    "res1.0_dp": "-r 1.0 --r_dp 0.2 --south_cutoff_row 2 --no_changing_meta",
 }
 QUICK = ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp"]
 

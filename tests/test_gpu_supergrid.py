@@ -1,0 +1,135 @@
+"""Whole-supergrid parity: the device build (plan -> in-place pieces) against the per-array sha256 of the six
+arrays the UNMODIFIED reference produced for its own CLI recipes (tests/golden/configs.json), the CLI + file
+round trip, row-slab (multi-GPU) decomposition, and size-independent properties at larger resolutions."""
+import numpy as np
+import pytest
+
+from util import assert_bits, sha
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ("x", "y", "dx", "dy", "area", "angle_dx")
+
+
+@pytest.fixture(scope="module")
+def SG():
+    from ocean_model_grid_generator_b200 import device, supergrid
+    device.ready()
+    return supergrid
+
+
+def _args(flags):
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    return vars(G._build_parser().parse_args(flags.split()))
+
+
+def _plan_args(a):
+    return {k: v for k, v in a.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta", "write_subgrid_files")}
+
+
+@pytest.mark.parametrize("name", ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp", "res0.25",
+                                  "res0.25_om5proto"])
+def test_config_matches_reference_hashes(SG, golden_configs, name):
+    if name not in golden_configs:
+        pytest.skip("no golden entry for %s" % name)
+    cfg = golden_configs[name]
+    plan = SG.plan_supergrid(**_plan_args(_args(cfg["flags"])))
+    got = SG.build_supergrid(plan).to_host()
+    for k in NAMES:
+        assert list(got[k].shape) == cfg["arrays"][k]["shape"], (k, got[k].shape)
+        assert sha(got[k]) == cfg["arrays"][k]["sha256"], "%s: array %s differs from the reference's" % (name, k)
+    total = float(np.sum(got["area"]))
+    assert abs(total - cfg["arrays"]["area"]["sum"]) <= 1e-12 * abs(total)       # global-area check, 1e-12 relative
+
+
+def test_cli_writes_reference_layout(SG, golden_configs, tmp_path):
+    from scipy.io import netcdf_file
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    cfg = golden_configs["res4.0"]
+    out = tmp_path / "ocean_hgrid_res4.0.nc"
+    G.cli(["-f", str(out)] + cfg["flags"].split() + ["--write_subgrid_files"])
+    f = netcdf_file(str(out), "r", mmap=False)
+    assert f.version_byte == 2
+    assert list(f.variables.keys()) == ["tile", "y", "x", "dy", "dx", "area", "angle_dx"]
+    assert list(f.dimensions.keys()) == ["nyp", "nxp", "ny", "nx", "string"]
+    for k in NAMES:
+        assert sha(f.variables[k][:]) == cfg["arrays"][k]["sha256"], k
+    assert f.variables["x"].units == b"degrees" and f.variables["dx"].units == b"meters" and f.variables["area"].units == b"m2"
+    assert b"".join(f.variables["tile"][:5]) == b"tile1"
+    for sub in ("Merc", "BP", "SO", "SC"):
+        assert (tmp_path / ("ocean_hgrid_res4.0.nc" + sub + ".nc")).exists()
+
+
+def test_cli_argument_errors(SG):
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    with pytest.raises(SystemExit) as e:
+        G.main(4, r_dp=0.2, lat_dp=-80.0, match_dy=[], grids="all")            # OGG:904-907
+    assert e.value.code == 2
+    with pytest.raises(SystemExit) as e:
+        G.main(4)                                                               # python defaults contain " sc" (OGG:870-888)
+    assert e.value.code == 2
+
+
+@pytest.mark.parametrize("flags,world", [("-r 1.0 --r_dp 0.2", 3), ("-r 0.25 --ensure_nj_even", 8), ("-r 2", 2)])
+def test_row_slabs_reassemble_to_whole(SG, flags, world):
+    """Each GPU's share (rank r of `world`) concatenated in rank order == the single-GPU supergrid, bit for bit."""
+    plan = SG.plan_supergrid(**_plan_args(_args(flags)))
+    whole = SG.build_supergrid(plan).to_host()
+    # ranks hold every piece's slab; reassemble piece by piece
+    parts = [SG.build_supergrid(plan, r, world) for r in range(world)]
+    hosts = [p.to_host() for p in parts]
+    area_total = sum(p.area_sum() for p in parts)
+    assert abs(area_total - whole["area"].sum()) <= 1e-12 * whole["area"].sum()
+    for k in NAMES:
+        rows = []
+        for pi in range(len(plan.pieces)):
+            for r in range(world):
+                c0, c1 = parts[r].slabs[pi]
+                off = sum(b - a for a, b in parts[r].slabs[:pi])
+                rows.append(hosts[r][k][off:off + (c1 - c0)])
+        if k in ("x", "y", "dx", "angle_dx"):
+            rows.append(hosts[world - 1][k][-1:])
+        assert_bits(np.concatenate(rows, axis=0), whole[k], "%s reassembled from %d slabs" % (k, world))
+
+
+def test_properties_quarter_degree(SG):
+    """BASELINE configs[1] (1/4 degree full tripolar, displaced pole): properties that need no oracle run."""
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 4 --r_dp 0.2")))
+    sg = SG.build_supergrid(plan)
+    a = sg.to_host()
+    assert a["x"].shape == (2243, 2881) and a["dx"].shape == (2243, 2880) and a["dy"].shape == (2242, 2881)
+    assert np.isfinite(a["area"]).all() and (a["area"] > 0).all() and (a["dx"] > 0).all() and (a["dy"] > 0).all()
+    assert a["angle_dx"].min() >= -90.0 and a["angle_dx"].max() <= 90.0
+    ycol = a["y"][:, plan.Ni // 4]
+    assert (np.diff(ycol) > 0).all() and np.searchsorted(ycol, 0.0) % 2 == 1       # OGG:1366-1370, :1425-1434
+    # bipolar fold symmetry: the last row is its own mirror image (y symmetric about the fold's centre)
+    top = a["y"][-1]
+    assert np.abs(top - top[::-1]).max() < 1e-9
+    # sphere area north of the doughnut edge: sum(area) = 2 pi Re^2 (1 - sin(lat_south)) up to the cap's quadrature error
+    Re = 6371.0e3
+    lat_s = a["y"][0, 0]
+    exact = 2 * np.pi * Re * Re * (1 - np.sin(np.deg2rad(-78.0)))               # bands + bipolar north of 78S (exact pieces)
+    j78 = plan.pieces[0].rows - 1
+    north = a["area"][j78:].sum()
+    assert abs(north - exact) / exact < 1e-12 * 50, (north, exact)
+    assert abs(sg.area_sum() - a["area"].sum()) <= 1e-12 * a["area"].sum()
+
+
+def test_eighth_degree_slabs_checksum(SG):
+    """BASELINE configs[2] (1/8 degree): 4 row-slabs == whole (sha256 per array), without any oracle run."""
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 8 --r_dp 0.2")))
+    assert (plan.nyp, plan.nxp) == (4485, 5761)
+    whole = SG.build_supergrid(plan).to_host()
+    world = 4
+    parts = [SG.build_supergrid(plan, r, world) for r in range(world)]
+    hosts = [p.to_host() for p in parts]
+    for k in NAMES:
+        rows = []
+        for pi in range(len(plan.pieces)):
+            for r in range(world):
+                c0, c1 = parts[r].slabs[pi]
+                off = sum(b - a for a, b in parts[r].slabs[:pi])
+                rows.append(hosts[r][k][off:off + (c1 - c0)])
+        if k in ("x", "y", "dx", "angle_dx"):
+            rows.append(hosts[world - 1][k][-1:])
+        assert sha(np.concatenate(rows, axis=0)) == sha(whole[k]), k

@@ -153,7 +153,7 @@ def test_cabi_exports_match_header():
     from ocean_model_grid_generator_b200 import _cabi
     lib = _cabi.load()
     header = open(os.path.join(ROOT, "include", "ogg_b200.h")).read()
-    declared = set(re.findall(r"^(?:int|const char\*)\s+(ogg_\w+)\s*\(", header, flags=re.M))
+    declared = set(re.findall(r"^(?:int|long long|const char\*)\s+(ogg_\w+)\s*\(", header, flags=re.M))
     assert declared, "no prototypes parsed"
     for name in declared:
         assert hasattr(lib, name), "symbol %s declared in ogg_b200.h is not exported" % name
@@ -181,3 +181,17 @@ def test_product_never_imports_oracle():
                 assert "ogg_oracle" not in src and "numpypi" not in src.replace("numpypi.numpypi_series", "").replace(
                     "numpypi_series", "") or f in ("devnp.py", "ocean_grid_generator.py", "__init__.py"), f
                 assert "import ogg_oracle" not in src and "libogg_oracle" not in src, f
+
+
+# ---- whole-supergrid composition of the oracle vs the reference-made per-array hashes -----------------
+@pytest.mark.parametrize("name,kw", [("res4.0", None), ("res1.0", dict(r=1.0, south_cutoff_row=2)),
+                                     ("res1.0_dp", dict(r=1.0, r_dp=0.2, south_cutoff_row=2)), ("res0.5", dict(r=2))])
+def test_oracle_supergrid_matches_reference_hashes(oracle, golden_configs, name, kw):
+    import supergrid_cpu
+    from util import sha
+    if kw is None:
+        pytest.skip("res4.0 uses --ensure_nj_even, outside supergrid_cpu's flag set")
+    got = supergrid_cpu.build_cpu(**kw)
+    for k, v in golden_configs[name]["arrays"].items():
+        assert list(got[k].shape) == v["shape"], (k, got[k].shape, v["shape"])
+        assert sha(got[k]) == v["sha256"], (name, k)
