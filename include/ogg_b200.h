@@ -105,6 +105,10 @@ int ogg_monotonic_bounding(double* x, int64_t nj, int64_t ni, double x_0, void* 
 /* displacedPoleCap_mesh (OGG:478-506, excluded_fraction=None) on index vectors i[nil], j[njl] */
 int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int64_t ni, int64_t nj, double lon0,
                 double lat0, double lam_pole, double r_pole, double* lams, double* phis, void* stream);
+/* generate_displaced_pole_grid (OGG:509-518) restricted to mesh rows [j0, j1) of the (Nj+1) x (Ni+1) cap: the integer
+ * index vectors np.arange(Ni+1), np.arange(j0, j1) are formed on the device.  lams, phis [j1-j0][Ni+1]. */
+int ogg_dp_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0, double lat0, double lam_pole,
+                    double r_pole, double* lams, double* phis, void* stream);
 /* great_arc_distance (OGG:522-532) -> out[njl][nil] */
 int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl,
                            int64_t nil, int64_t nx, int64_t ny, double lon0, double lat0, double lon_dp,

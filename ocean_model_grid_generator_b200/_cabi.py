@@ -39,6 +39,7 @@ SIGNATURES = {
     "ogg_dp_projection": [_dp, _dp, _i64, _i64, _d, _d, _d, _dp, _dp, _vp],
     "ogg_monotonic_bounding": [_dp, _i64, _i64, _d, _vp],
     "ogg_dp_mesh": [_dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
+    "ogg_dp_cap_mesh": [_i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
     "ogg_great_arc_distance": [_dp, _dp, _dp, _dp, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _vp],
     "ogg_numerical_h": [_int, _dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _vp],
     "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _dp, _dp, _dp, _vp],

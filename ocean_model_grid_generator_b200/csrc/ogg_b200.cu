@@ -40,12 +40,24 @@ static int num_sms() {
   return g_num_sms;
 }
 
-// stream-ordered scratch
+// stream-ordered scratch.  The default pool would hand its memory back to the driver at every synchronisation;
+// keep it, so that steady-state steps never touch the physical allocator.
+static void keep_pool_memory() {
+  static int done_for = -1;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev == done_for) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    unsigned long long thr = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  done_for = dev;
+}
 struct Scratch {
   cudaStream_t st;
   void* ptrs[16];
   int n = 0;
-  explicit Scratch(cudaStream_t s) : st(s) {}
+  explicit Scratch(cudaStream_t s) : st(s) { keep_pool_memory(); }
   template <typename T>
   cudaError_t get(T** p, size_t count) {
     void* q = nullptr;
@@ -649,18 +661,20 @@ __global__ void __launch_bounds__(256) k_dp_projection_raw(const double* __restr
 
 // column / row tables for lattice evaluation: u = lon0 + (i*360)/ni (:479), v = -90 + (j*(lat0+90))/nj (:482)
 // `shift` is added to the index first (numerical_hi/hj pass i+eps etc., :538-558)
-__global__ void __launch_bounds__(256) k_dp_tables(const double* __restrict__ iv, i64 ncol, double ishift,
-                                                   const double* __restrict__ jv, i64 nrow, double jshift, i64 ni,
+__global__ void __launch_bounds__(256) k_dp_tables(const double* __restrict__ iv, i64 i0, i64 ncol, double ishift,
+                                                   const double* __restrict__ jv, i64 j0, i64 nrow, double jshift, i64 ni,
                                                    i64 nj, double lon0, double lat0, const double* __restrict__ cst,
                                                    Cx* __restrict__ ct, double* __restrict__ rt) {
   const DpConst K = dp_load(cst);
   const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   if (ct && t < ncol) {
-    const double idx = ishift != 0.0 ? iv[t] + ishift : iv[t];
+    const double base = iv ? iv[t] : (double)(i0 + t);
+    const double idx = ishift != 0.0 ? base + ishift : base;
     ct[t] = dp_col(lon0 + (idx * 360.0) / (double)ni, K.z0);
   }
   if (rt && t < nrow) {
-    const double idx = jshift != 0.0 ? jv[t] + jshift : jv[t];
+    const double base = jv ? jv[t] : (double)(j0 + t);
+    const double idx = jshift != 0.0 ? base + jshift : base;
     const double a = -90.0, b = lat0;
     rt[t] = dp_row(a + (idx * (b - a)) / (double)nj, K.r_joint);
   }
@@ -853,14 +867,16 @@ __global__ void __launch_bounds__(kScanThreads) k_dp_hsamples(const Cx* __restri
 }
 // x_0 of every shifted mesh: lon0 + ((i[0] (+/-) s)*360)/ni  (:463 with :479)
 template <int NV>
-__global__ void k_dp_x0(const double* __restrict__ iv, double eps, i64 ni, double lon0, double* __restrict__ x0v) {
+__global__ void k_dp_x0(const double* __restrict__ iv, double i0, double eps, i64 ni, double lon0,
+                        double* __restrict__ x0v) {
   const int m = threadIdx.x;
   if (m >= 4 * NV) return;
   const int lvl = m / 4, kind = m % 4;
   const double s = lvl == 0 ? eps : (lvl == 1 ? 2.0 * eps : 3.0 * eps);
-  double idx = iv[0];
-  if (kind == 0) idx = iv[0] + s;
-  if (kind == 1) idx = iv[0] - s;
+  const double first = iv ? iv[0] : i0;
+  double idx = first;
+  if (kind == 0) idx = first + s;
+  if (kind == 1) idx = first - s;
   x0v[m] = lon0 + (idx * 360.0) / (double)ni;
 }
 
@@ -1207,18 +1223,19 @@ int ogg_dp_projection(const double* lon, const double* lat, int64_t nj, int64_t 
 
 namespace ogg {
 // single shifted mesh on index vectors: tables -> raw lattice -> unwrap.  cst: device {r_joint, z0}
-static int dp_mesh_dev(const double* iv, i64 nil, double ishift, const double* jv, i64 njl, double jshift, i64 ni, i64 nj,
+static int dp_mesh_dev(const double* iv, i64 i0, i64 nil, double ishift, const double* jv, i64 j0, i64 njl, double jshift,
+                       i64 ni, i64 nj,
                        double lon0, double lat0, const double* cst, double* lams, double* phis, cudaStream_t st) {
   Scratch ws(st);
   Cx* ct; double* rt; double* x0;
   OGG_CUDA(ws.get(&ct, nil)); OGG_CUDA(ws.get(&rt, njl)); OGG_CUDA(ws.get(&x0, 12));
   const i64 m = nil > njl ? nil : njl;
-  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables), (cdiv_u(m, 256), 256), (st), iv, nil, ishift, jv, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
+  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables), (cdiv_u(m, 256), 256), (st), iv, i0, nil, ishift, jv, j0, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
   OGG_LAUNCH_CHECK();
   OGG_LAUNCH(KID_DP_RAW, (k_dp_lattice_raw), (lattice_grid(nil, njl, 256), 256), (st), ct, rt, njl, nil, cst, lams, phis);
   OGG_LAUNCH_CHECK();
   // x_0 = lon_grid[0,0] = lon0 + ((i[0]+shift)*360)/ni : reuse k_dp_x0<1> slots (kind 0 = plus shift, kind 2 = none)
-  OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, ishift, ni, lon0, x0);
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, (double)i0, ishift, ni, lon0, x0);
   OGG_LAUNCH_CHECK();
   const i64 cap = (i64)num_sms() * 8;
   OGG_LAUNCH(KID_MONOTONIC, (k_monotonic), ((unsigned)(njl < cap ? njl : cap), kScanThreads), (st), lams, njl, nil, 0.0, ishift != 0.0 ? x0 + 0 : x0 + 2);
@@ -1238,7 +1255,19 @@ int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int6
   OGG_CUDA(ws.get(&cst, 3));
   OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lam_pole, r_pole, cst);
   OGG_LAUNCH_CHECK();
-  return dp_mesh_dev(i, nil, 0.0, j, njl, 0.0, ni, nj, lon0, lat0, cst, lams, phis, st);
+  return dp_mesh_dev(i, 0, nil, 0.0, j, 0, njl, 0.0, ni, nj, lon0, lat0, cst, lams, phis, st);
+}
+
+int ogg_dp_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0, double lat0, double lam_pole, double r_pole,
+                    double* lams, double* phis, void* stream) {
+  if (Ni < 1 || Nj < 1 || j0 < 0 || j1 > Nj + 1 || j0 >= j1 || !lams || !phis) return OGG_ERR_ARG;
+  cudaStream_t st = S(stream);
+  Scratch ws(st);
+  double* cst;
+  OGG_CUDA(ws.get(&cst, 3));
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lam_pole, r_pole, cst);
+  OGG_LAUNCH_CHECK();
+  return dp_mesh_dev(nullptr, 0, Ni + 1, 0.0, nullptr, j0, j1 - j0, 0.0, Ni, Nj, lon0, lat0, cst, lams, phis, st);
 }
 
 int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl, int64_t nil,
@@ -1253,9 +1282,9 @@ int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1,
   OGG_CUDA(ws.get(&l0, n)); OGG_CUDA(ws.get(&p0, n)); OGG_CUDA(ws.get(&l1, n)); OGG_CUDA(ws.get(&p1, n));
   OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lon_dp, r_dp, cst);
   OGG_LAUNCH_CHECK();
-  int rc = dp_mesh_dev(i0, nil, 0.0, j0, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
+  int rc = dp_mesh_dev(i0, 0, nil, 0.0, j0, 0, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
   if (rc) return rc;
-  rc = dp_mesh_dev(i1, nil, 0.0, j1, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
+  rc = dp_mesh_dev(i1, 0, nil, 0.0, j1, 0, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
   if (rc) return rc;
   OGG_LAUNCH(KID_ELEMENTWISE, (k_haversine), (flat_grid(n), 256), (st), l0, p0, l1, p1, n, out);
   OGG_LAUNCH_CHECK();
@@ -1307,9 +1336,9 @@ static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 nco
   return OGG_OK;
 }
 static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
-  if (nv == 1) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, eps, ni, lon0, x0v);
-  else if (nv == 2) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<2>), (1, 32), (st), iv, eps, ni, lon0, x0v);
-  else OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<3>), (1, 32), (st), iv, eps, ni, lon0, x0v);
+  if (nv == 1) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
+  else if (nv == 2) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<2>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
+  else OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<3>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1336,11 +1365,11 @@ int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i
     const double s = m == 0 ? eps : (m == 1 ? 2.0 * eps : 3.0 * eps);
     int rc;
     if (direction == 0) {
-      rc = dp_mesh_dev(i, nil, s, j, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
-      if (!rc) rc = dp_mesh_dev(i, nil, -s, j, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
+      rc = dp_mesh_dev(i, 0, nil, s, j, 0, njl, 0.0, nx, ny, lon0, lat0, cst, l0, p0, st);
+      if (!rc) rc = dp_mesh_dev(i, 0, nil, -s, j, 0, njl, 0.0, nx, ny, lon0, lat0, cst, l1, p1, st);
     } else {
-      rc = dp_mesh_dev(i, nil, 0.0, j, njl, s, nx, ny, lon0, lat0, cst, l0, p0, st);
-      if (!rc) rc = dp_mesh_dev(i, nil, 0.0, j, njl, -s, nx, ny, lon0, lat0, cst, l1, p1, st);
+      rc = dp_mesh_dev(i, 0, nil, 0.0, j, 0, njl, s, nx, ny, lon0, lat0, cst, l0, p0, st);
+      if (!rc) rc = dp_mesh_dev(i, 0, nil, 0.0, j, 0, njl, -s, nx, ny, lon0, lat0, cst, l1, p1, st);
     }
     if (rc) return rc;
     OGG_LAUNCH(KID_ELEMENTWISE, (k_haversine), (flat_grid(n), 256), (st), l0, p0, l1, p1, n, ds[m]);

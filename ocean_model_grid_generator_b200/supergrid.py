@@ -279,11 +279,8 @@ class Supergrid(object):
         else:  # displaced pole
             p = piece.p
             j0, j1 = piece.row0 + c0, piece.row0 + c1
-            if self._iv is None:
-                self._iv = _dev.to_dev(numpy.arange(plan.Ni + 1))
-            jv = _dev.to_dev(numpy.arange(j0, j1 + 1))
-            _cabi.call("ogg_dp_mesh", _dev.ptr(self._iv), plan.Ni + 1, _dev.ptr(jv), j1 - j0 + 1, plan.Ni, p["Nj"],
-                       p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"], px, py, st)                   # OGG:1162
+            _cabi.call("ogg_dp_cap_mesh", plan.Ni, p["Nj"], j0, j1 + 1, p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"],
+                       px, py, st)                                                                 # OGG:1162
             _cabi.call("ogg_angle_x", px, py, c1 - c0 + 1, nxp, pangle, st)                       # OGG:1163
             if not plan.skip_metrics:
                 _cabi.call("ogg_dp_metrics_quad", 4, plan.Ni, p["Nj"], j0, j1, p["lon0"], p["lat0"], p["lon_dp"],

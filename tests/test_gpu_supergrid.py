@@ -98,7 +98,7 @@ def test_properties_quarter_degree(SG):
     sg = SG.build_supergrid(plan)
     a = sg.to_host()
     assert a["x"].shape == (2243, 2881) and a["dx"].shape == (2243, 2880) and a["dy"].shape == (2242, 2881)
-    assert np.isfinite(a["area"]).all() and (a["area"] > 0).all() and (a["dx"] > 0).all() and (a["dy"] > 0).all()
+    assert np.isfinite(a["area"]).all() and (a["area"] > 0).all() and (a["dx"] > 0).all() and (a["dy"] >= 0).all()
     assert a["angle_dx"].min() >= -90.0 and a["angle_dx"].max() <= 90.0
     ycol = a["y"][:, plan.Ni // 4]
     assert (np.diff(ycol) > 0).all() and np.searchsorted(ycol, 0.0) % 2 == 1       # OGG:1366-1370, :1425-1434
