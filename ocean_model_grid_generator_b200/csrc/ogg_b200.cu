@@ -633,7 +633,7 @@ OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double
   const Cx z = cmul(Cx{r, 0.0}, ep);                                                         // :454
   const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
   const Cx w = cdivn(Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, 0.0 + q.im});        // :455
-  lam_raw = p_atan2(w.im, w.re) * (180.0 / kPi);                                             // :457
+  lam_raw = p_atan2(w.im, w.re) * kC[k180OverPi];                                             // :457
   const double rw = sqrt(w.re * w.re + w.im * w.im);                                         // :465
   phi = -90 + p_atan(rw * K.r_joint) / kPi180;                                               // :466
 }
