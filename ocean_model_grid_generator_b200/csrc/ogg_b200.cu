@@ -79,11 +79,11 @@ struct Scratch {
 // kernel's own duration inside the timed region.
 // ------------------------------------------------------------------------------------------------
 enum KernelId { KID_ELEMENTWISE, KID_BAND_TABLES, KID_BAND_FILL, KID_MIDAS, KID_ANGLE, KID_BP_PROJECTION, KID_BP_TABLES,
-                KID_BP_MESH, KID_BP_SAMPLES, KID_SAMPLE_INDEX, KID_QUAD, KID_DP_SETUP, KID_DP_TABLES, KID_DP_RAW,
+                KID_BP_MESH, KID_BP_SAMPLES, KID_BP_QUAD, KID_SAMPLE_INDEX, KID_QUAD, KID_DP_SETUP, KID_DP_TABLES, KID_DP_RAW,
                 KID_MONOTONIC, KID_DP_HSAMPLES, KID_REDUCE, KID_COUNT };
 static const char* const kKernelNames[KID_COUNT] = {
     "elementwise", "band_tables", "band_fill", "midas", "angle_x", "bipolar_projection", "bipolar_tables", "bipolar_mesh",
-    "bipolar_samples", "sample_index", "quad_cells", "dp_setup", "dp_tables", "dp_raw", "monotonic_bounding", "dp_hsamples",
+    "bipolar_samples", "bipolar_quad_fused", "sample_index", "quad_cells", "dp_setup", "dp_tables", "dp_raw", "monotonic_bounding", "dp_hsamples",
     "reduce"};
 static long long g_launches = 0;
 static bool g_timing = false;
@@ -576,6 +576,107 @@ __global__ void __launch_bounds__(128) k_quad_cells(const double* __restrict__ s
   }
 }
 
+// --- fused bipolar quadrature (OGG:136-188): samples never leave the SM ------------------------------------------
+// Sample index of unique position u for cells [c0, c1) (same law as k_sample_index).
+OGG_DI double sample_index_at(const QuadNodes& q, int n, i64 c0, i64 c1, i64 total, int fudge, i64 u) {
+  const i64 nu = (n - 1) * (c1 - c0) + 1;
+  if (u >= nu) return q.b[0] * (double)total + q.a[0] * (double)(total + 1);  // the exact pole row (:183 at j=ny)
+  i64 c = c0 + u / (n - 1);
+  int k = (int)(u % (n - 1));
+  if (u == nu - 1) { c = c1 - 1; k = n - 1; }
+  double v = q.b[k] * (double)c + q.a[k] * (double)(c + 1);                    // :145,:155
+  if (fudge && u == nu - 1 && v == (double)total) v = (double)total - 0.001;   // :146-147
+  return v;
+}
+// column table over all unique sample columns, row table over the unique sample rows of cell rows [j0, j1)
+// (+ the exact pole row when j1 == ny): one launch replaces k_sample_index x2 + k_bp_tables x2.
+__global__ void __launch_bounds__(256) k_bp_quad_tables(QuadNodes q, int n, i64 nx, i64 ny, i64 j0, i64 j1, i64 nuc,
+                                                        i64 nur, double lat0_bp, double lon_bp, double rp,
+                                                        BpCol* __restrict__ ct, BpRow* __restrict__ rt) {
+  const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (t < nuc) {
+    const double idx = sample_index_at(q, n, 0, nx, nx, 0, t);
+    ct[t] = bp_col(lon_bp + (idx * 360.0) / (double)nx, lon_bp);                 // :126
+  }
+  if (t < nur) {
+    const double idx = sample_index_at(q, n, j0, j1, ny, 1, t);
+    rt[t] = bp_row(lat0_bp + (idx * (90 - lat0_bp)) / (double)ny, rp);           // :127
+  }
+}
+
+// One block = a tile of TR x TC cells.  Phase 1: the tile's unique samples ((N-1)TR+1) x ((N-1)TC+1) of the scaled
+// h_i_inv, h_j_inv (:130-132) go to shared memory, columns stored residue-major (column c at
+// (c mod (N-1))*(TC+1) + c/(N-1)) so that phase 2 -- one thread per cell, sums in the reference's order
+// (:180-187) -- reads consecutive words across a warp.  Samples on tile edges are recomputed by the neighbour
+// (3.9 % more samples at TR=8, TC=32) instead of travelling through HBM (16 B written + 16 B read per sample).
+template <int N, int TR, int TC>
+__global__ void __launch_bounds__(256) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt, i64 nuc,
+                                                       i64 ncr, i64 nx, i64 ny, double lat0_bp, double lon_bp, double rp,
+                                                       double Re, double* __restrict__ dxq, double* __restrict__ dyq,
+                                                       double* __restrict__ daq) {
+  constexpr int SR = (N - 1) * TR + 1, SC = (N - 1) * TC + 1, SCP = (N - 1) * (TC + 1);
+  extern __shared__ double smem[];
+  double* sx = smem;
+  double* sy = smem + SR * SCP;
+  const i64 gr0 = (i64)blockIdx.y * TR * (N - 1), gc0 = (i64)blockIdx.x * TC * (N - 1);
+  const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
+  for (int s = threadIdx.x; s < SR * SC; s += 256) {
+    const int r = s / SC, c = s - r * SC;
+    const i64 gr = gr0 + r, gc = gc0 + c;
+    double a = 0.0, b = 0.0;
+    if (gr < nreg && gc < nuc) {
+      double l, p;
+      bp_sample<false>(rt[gr], ct[gc], lon_bp, rp, l, p, a, b);
+      a = ((a * 2) * kPi) / (double)nx;                                           // :131
+      b = ((b * (90 - lat0_bp)) * kPi180) / (double)ny;                           // :132
+    }
+    const int pos = r * SCP + (c % (N - 1)) * (TC + 1) + c / (N - 1);
+    sx[pos] = a;
+    sy[pos] = b;
+  }
+  __syncthreads();
+  const int lr = threadIdx.x / TC, li = threadIdx.x - lr * TC;
+  const i64 j = (i64)blockIdx.y * TR + lr, i = (i64)blockIdx.x * TC + li;
+  if (lr >= TR || j >= ncr || i >= nx) return;
+  const int r0 = (N - 1) * lr;
+  // sample column (N-1)*li + k sits at residue k, slot li (k < N-1) or residue 0, slot li+1 (k = N-1)
+  auto at = [&](const double* a, int jj, int k) -> double {
+    return a[(r0 + jj) * SCP + (k == N - 1 ? li + 1 : k * (TC + 1) + li)];
+  };
+  double prod[N][N], row[N], col[N];
+#pragma unroll
+  for (int jj = 0; jj < N; ++jj)
+#pragma unroll
+    for (int k = 0; k < N; ++k) prod[jj][k] = at(sx, jj, k) * at(sy, jj, k);      // :178
+#pragma unroll
+  for (int k = 0; k < N; ++k) { row[k] = at(sx, 0, k); col[k] = at(sy, k, 0); }
+  daq[j * nx + i] = (quad_avg_2d<N>(prod) * Re) * Re;                             // :182,:185
+  dxq[j * nx + i] = quad_avg_1d<N>(row) * Re;                                     // :183,:186
+  dyq[j * (nx + 1) + i] = quad_avg_1d<N>(col) * Re;                               // :184,:187
+  if (i == nx - 1) {                                                              // dyq has nx+1 columns
+#pragma unroll
+    for (int k = 0; k < N; ++k) col[k] = at(sy, k, N - 1);
+    dyq[j * (nx + 1) + nx] = quad_avg_1d<N>(col) * Re;
+  }
+}
+// dxq[ny, :] (:183 at the ghost row j = ny, kept by :186): quadrature of the scaled h_i_inv along the exact pole row
+template <int N>
+__global__ void __launch_bounds__(128) k_bp_pole_row(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt,
+                                                     i64 top_row, i64 nx, double lon_bp, double rp, double Re,
+                                                     double* __restrict__ dxq_row) {
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i >= nx) return;
+  const BpRow R = rt[top_row];
+  double v[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    double l, p, a, b;
+    bp_sample<false>(R, ct[(N - 1) * i + k], lon_bp, rp, l, p, a, b);
+    v[k] = ((a * 2) * kPi) / (double)nx;
+  }
+  dxq_row[i] = quad_avg_1d<N>(v) * Re;
+}
+
 template <int N>
 __global__ void __launch_bounds__(128) k_quad_avg(const double* __restrict__ y, i64 m, double* __restrict__ out) {
   const i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x;
@@ -961,6 +1062,34 @@ static int run_quad_cells(int order, const double* sx, const double* sy, i64 nuc
                      nuc, ncr, nx, top_row, Re, dxq, dyq, daq);
 }
 
+constexpr int kBpTileRows = 8, kBpTileCols = 32;
+template <int N>
+static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
+                                double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
+                                cudaStream_t st) {
+  constexpr int TR = kBpTileRows, TC = kBpTileCols;
+  static_assert(TR * TC <= 256, "one thread per cell");
+  constexpr size_t smem = sizeof(double) * 2 * ((N - 1) * TR + 1) * ((N - 1) * (TC + 1));
+  static bool configured = false;
+  if (!configured) {
+    OGG_CUDA(cudaFuncSetAttribute(k_bp_quad_fused<N, TR, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const dim3 g(cdiv_u(nx, TC), cdiv_u(ncr, TR));
+  launch_begin(KID_BP_QUAD, st);
+  k_bp_quad_fused<N, TR, TC><<<g, 256, smem, st>>>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq);
+  launch_end(st);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+static int run_bp_quad_fused(int order, const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
+                             double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq, cudaStream_t st) {
+  if (order == 2) return launch_bp_quad_fused<2>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (order == 3) return launch_bp_quad_fused<3>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (order == 4) return launch_bp_quad_fused<4>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  return launch_bp_quad_fused<5>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+}
+
 // cap on the per-chunk sample scratch of the quadrature drivers (bytes of dx+dy samples)
 static const i64 kQuadChunkBytes = (i64)1 << 30;
 
@@ -1135,34 +1264,22 @@ int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, 
   if (quad_nodes_host(order, &q)) return OGG_ERR_UNCODED_ORDER;
   if (nx < 1 || ny < 1 || j0 < 0 || j1 > ny || j0 >= j1 || !dxq || !dyq || !daq) return OGG_ERR_ARG;
   cudaStream_t st = S(stream);
+  const bool top = j1 == ny;
+  const i64 ncr = j1 - j0;
   const i64 nuc = (order - 1) * nx + 1;
-  i64 rows_per_chunk = kQuadChunkBytes / (16 * nuc * (order - 1));
-  if (rows_per_chunk < 1) rows_per_chunk = 1;
+  const i64 nur = (order - 1) * ncr + 1 + (top ? 1 : 0);  // + the exact pole row
   Scratch ws(st);
-  const i64 max_cr = rows_per_chunk < (j1 - j0) ? rows_per_chunk : (j1 - j0);
-  const i64 max_nur = (order - 1) * max_cr + 2;
-  double *iv, *jv, *sx, *sy;
   BpCol* ct; BpRow* rt;
-  OGG_CUDA(ws.get(&iv, nuc)); OGG_CUDA(ws.get(&jv, max_nur));
-  OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, max_nur));
-  OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
-  OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nuc + 1, 256), 256), (st), q, order, 0, nx, nx, 0, iv);
+  OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, nur));
+  const i64 m = nuc > nur ? nuc : nur;
+  OGG_LAUNCH(KID_BP_TABLES, (k_bp_quad_tables), (cdiv_u(m, 256), 256), (st), q, order, nx, ny, j0, j1, nuc, nur, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
-  OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(nuc, 256), 256), (st), iv, 0, nuc, nullptr, 0, 0, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
-  OGG_LAUNCH_CHECK();
-  for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
-    const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
-    const bool top = c1 == ny;
-    const i64 nur = (order - 1) * (c1 - c0) + 1 + (top ? 1 : 0);
-    OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nur + 1, 256), 256), (st), q, order, c0, c1, ny, 1, jv);   // :144-151
-    OGG_LAUNCH_CHECK();
-    OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(nur, 256), 256), (st), nullptr, 0, 0, jv, 0, nur, nx, ny, lat0_bp, lon_bp, rp, ct, rt);
-    OGG_LAUNCH_CHECK();
-    OGG_LAUNCH(KID_BP_SAMPLES, (k_bp_lattice<1>), (lattice_grid(nuc, nur, 256), 256), (st), ct, rt, nur, nuc, nx, ny, 0, lat0_bp, lon_bp, rp, sx, sy,
-                                                                 nullptr, nullptr);
-    OGG_LAUNCH_CHECK();
-    int rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
-                            dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
+  int rc = run_bp_quad_fused(order, ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (rc) return rc;
+  if (top) {
+    const dim3 g(cdiv_u(nx, 128)), b(128);
+    rc = launch_quad(order, k_bp_pole_row<2>, k_bp_pole_row<3>, k_bp_pole_row<4>, k_bp_pole_row<5>, g, b, st,
+                     (const BpCol*)ct, (const BpRow*)rt, nur - 1, (i64)nx, lon_bp, rp, Re, dxq + ncr * nx);
     if (rc) return rc;
   }
   return OGG_OK;
