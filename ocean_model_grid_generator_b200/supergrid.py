@@ -198,11 +198,7 @@ def first_column_latitudes(piece):
 # --------------------------------------------------------------------------------------------------
 # device build
 # --------------------------------------------------------------------------------------------------
-def slab_bounds(ncells, rank, world):
-    """Contiguous split of a piece's cell rows over `world` ranks (every rank gets a share of every piece)."""
-    base, rem = divmod(ncells, world)
-    c0 = rank * base + min(rank, rem)
-    return c0, c0 + base + (1 if rank < rem else 0)
+from .slabs import slab_bounds  # noqa: E402  (contiguous split of a piece's cell rows; every rank gets a share of every piece)
 
 
 class Supergrid(object):
