@@ -64,7 +64,28 @@ class ClockSampler(object):
     def __init__(self, index):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
 
+    def _run_nvml(self):
+        """Fast path: NVML samples every ~2 ms, so that even a 30 ms timed region gets several clock samples."""
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(self.index)
+        mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+        bits = (("hw_slowdown", N.nvmlClocksThrottleReasonHwSlowdown),
+                ("hw_thermal_slowdown", N.nvmlClocksThrottleReasonHwThermalSlowdown),
+                ("sw_thermal_slowdown", N.nvmlClocksThrottleReasonSwThermalSlowdown),
+                ("sw_power_cap", N.nvmlClocksThrottleReasonSwPowerCap))
+        while not self._stop.is_set():
+            sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
+            rs = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self.samples.append([str(sm), str(mx)] + ["Active" if rs & b else "Not Active" for _, b in bits])
+            self._stop.wait(0.002)
+
     def _run(self):
+        try:
+            self._run_nvml()
+            return
+        except Exception:
+            pass
         while not self._stop.is_set():
             try:
                 out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -190,7 +211,7 @@ def run_ours(args):
     # ---- timed region: K steps, CUDA events on the launching stream, per-kernel events inside --------------
     sampler = ClockSampler(local)
     lib.ogg_timing_reset()
-    lib.ogg_timing_enable(1)
+    lib.ogg_timing_enable(2)     # event brackets around the three heavy kernel classes only (6 launches of ~26 per step)
     l0 = lib.ogg_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()
@@ -210,13 +231,24 @@ def run_ours(args):
     ms = float(t[0])
     value = npoints * args.steps / (ms * 1e-3)
 
-    kern = {}
-    for k in range(lib.ogg_timing_kernels()):
-        tot, n = ctypes.c_double(), ctypes.c_longlong()
-        lib.ogg_timing_get(k, ctypes.byref(tot), ctypes.byref(n))
-        if n.value:
-            kern[lib.ogg_timing_name(k).decode()] = (tot.value, n.value)
-    lib.ogg_timing_reset()
+    def read_kernels():
+        out = {}
+        for k in range(lib.ogg_timing_kernels()):
+            tot, n = ctypes.c_double(), ctypes.c_longlong()
+            lib.ogg_timing_get(k, ctypes.byref(tot), ctypes.byref(n))
+            if n.value:
+                out[lib.ogg_timing_name(k).decode()] = (tot.value, n.value)
+        lib.ogg_timing_reset()
+        return out
+
+    kern = read_kernels()
+    # second, untimed-for-the-metric pass with a bracket around EVERY launch: the per-kernel table
+    lib.ogg_timing_enable(1)
+    for _ in range(args.steps):
+        step()
+    barrier()
+    lib.ogg_timing_enable(0)
+    kern_all = read_kernels()
 
     # ---- end to end through the public API: plan + H2D of the 1-D laws + build + D2H of the six arrays ------
     e2e = None
@@ -276,7 +308,7 @@ def run_ours(args):
             units["band_fill"] = units.get("band_fill", 0) + (c1 - c0) * plan.nxp
     dom = max(kern, key=lambda k: kern[k][0]) if kern else None
     roof = None
-    kernels_ms = {k: round(v[0] / args.steps, 4) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])}
+    kernels_ms = {k: round(v[0] / args.steps, 4) for k, v in sorted(kern_all.items(), key=lambda kv: -kv[1][0])}
     if dom in ("dp_hsamples", "bipolar_samples"):
         ops = OPS_DP_SAMPLE if dom == "dp_hsamples" else OPS_BP_SAMPLE
         per_step_ms = kern[dom][0] / args.steps
@@ -309,7 +341,8 @@ def run_ours(args):
                                 % (npoints * 48 / 1e6),
                        "global_area_m2": total_area},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "roofline_band_hbm": roof_hbm,
-            "kernels_ms_per_step": kernels_ms, "fp64_issue_peak_tflops_measured": fp64_peak_tf}
+            "kernels_ms_per_step_all_launches_bracketed_pass": kernels_ms,
+            "kernels_ms_per_step_timed_region": {k: round(v[0] / args.steps, 4) for k, v in kern.items()}, "fp64_issue_peak_tflops_measured": fp64_peak_tf}
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(r, args.r_dp)
     elif world > 1:

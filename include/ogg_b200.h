@@ -128,7 +128,8 @@ int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, voi
 /* ---- launch accounting (bench.py: gpu_launches and per-kernel CUDA-event durations) ---------------------------------- */
 /* kernels launched by this library since it was loaded */
 long long ogg_launch_count(void);
-/* when on, every launch is bracketed by CUDA events on its own stream */
+/* on = 1: every launch is bracketed by CUDA events on its own stream; on = 2: only the heavy kernel classes
+   (dp_hsamples, bipolar_quad_fused, band_fill), so that the brackets do not perturb a timed step; 0: off */
 int ogg_timing_enable(int on);
 int ogg_timing_reset(void);
 int ogg_timing_kernels(void);          /* number of kernel classes */

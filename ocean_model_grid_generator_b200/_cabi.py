@@ -63,7 +63,8 @@ class OggError(RuntimeError):
 
 
 def library_path():
-    return _build.LIB
+    # OGG_B200_LIB: developer knob for A/B-timing another build of the same sources (tools/kbench.py); still a CUDA library
+    return os.environ.get("OGG_B200_LIB") or _build.LIB
 
 
 def load(build_if_missing=True):

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "../../include/ogg_b200.h"
@@ -86,7 +87,8 @@ static const char* const kKernelNames[KID_COUNT] = {
     "bipolar_samples", "bipolar_quad_fused", "sample_index", "quad_cells", "dp_setup", "dp_tables", "dp_raw", "monotonic_bounding", "dp_hsamples",
     "reduce"};
 static long long g_launches = 0;
-static bool g_timing = false;
+static int g_timing = 0;         // 0 off, 1 every launch, 2 only the heavy kernel classes (caps + band fill)
+static bool g_timed_this = false;
 struct TimedLaunch { int id; cudaEvent_t e0, e1; };
 static std::vector<TimedLaunch> g_timed;
 static std::vector<cudaEvent_t> g_event_pool;
@@ -98,14 +100,15 @@ static cudaEvent_t take_event() {
 }
 static inline void launch_begin(int id, cudaStream_t st) {
   ++g_launches;
-  if (g_timing) {
+  g_timed_this = g_timing == 1 || (g_timing == 2 && (id == KID_DP_HSAMPLES || id == KID_BP_QUAD || id == KID_BAND_FILL));
+  if (g_timed_this) {
     TimedLaunch t{id, take_event(), take_event()};
     cudaEventRecord(t.e0, st);
     g_timed.push_back(t);
   }
 }
 static inline void launch_end(cudaStream_t st) {
-  if (g_timing) cudaEventRecord(g_timed.back().e1, st);
+  if (g_timed_this) cudaEventRecord(g_timed.back().e1, st);
 }
 template <typename K, typename... A>
 static inline void launch_cfg(cudaStream_t st, dim3 g, dim3 b, K k, A... a) {
@@ -886,83 +889,125 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
 }
 
 // --- fused numerical_hi + numerical_hj on a lattice of unique samples (OGG:583-584) ------------------------------
-// One block per sample row sweeping the row in tiles of kScanThreads columns.  For finite-difference order
-// 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column), each needing its own
-// longitude unwrap along the row: their 2-state maps are packed into one word and scanned together; the
-// carry (previous raw longitude and shift state per mesh) moves from tile to tile through shared memory.
-// Column table ct: [ncol][1+2NV] = e' at {i, i+eps, i-eps, i+2eps, i-2eps, ...}; row table rt: [nrow][1+2NV] likewise.
-template <int NV>
-__global__ void __launch_bounds__(kScanThreads) k_dp_hsamples(const Cx* __restrict__ ct, const double* __restrict__ rt,
-                                                              i64 nrow, i64 ncol, const double* __restrict__ x0v,
-                                                              const double* __restrict__ cst, double reps,
-                                                              double* __restrict__ hx, double* __restrict__ hy) {
-  constexpr int NM = 4 * NV;       // meshes
-  constexpr int NT = 1 + 2 * NV;   // table entries per row / column
-  __shared__ double raw[NM][kScanThreads + 1];
-  __shared__ unsigned sh[2 * (kScanThreads / 32)];
-  __shared__ unsigned s_carry;
-  __shared__ double rrow[NT];
+// For finite-difference order 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column),
+// each needing its own longitude unwrap along the row: their 2-state maps are packed into one word and scanned
+// together.  Column table ct: [ncol][1+2NV] = e' at {i, i+eps, i-eps, i+2eps, i-2eps, ...}; row table rt likewise.
+//
+// Work item = (sample row, tile of THREADS-1 new columns); item k belongs to CTA k mod gridDim.x of a grid that is
+// co-resident by construction (cooperative launch, one CTA per occupancy slot), so the load is balanced for ANY
+// number of sample rows -- a row-slab on one of 8 GPUs has far fewer rows than there are CTA slots.  Thread 0 of a
+// tile re-evaluates the previous tile's last column (the predecessor raw longitudes of thread 1), so a tile needs
+// from its left neighbours only the shift STATE (one bit per mesh) after that column: a decoupled look-back.  Each
+// tile publishes a 64-bit descriptor: first its aggregate 2-state map, then -- once the state at its left edge is
+// known -- the state after its last column; a tile resolves its left-edge state by walking back over aggregates until
+// it meets a published state (tile 0 of a row knows its state: not shifted).  Every CTA works through its items in
+// increasing order and waits only on lower-numbered items, so the lowest unfinished item can always proceed.
+constexpr unsigned long long kDescAgg = 1ull << 62, kDescState = 2ull << 62;
+OGG_DI unsigned long long desc_load(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+OGG_DI void desc_store(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// The 4*NV projected meshes of a thread's column are parked in shared memory and the per-mesh work runs in partly
+// rolled loops: fewer live registers, and less code than the fully unrolled form (which misses the instruction cache).
+// Items are numbered tile-major (all rows' tile t before any tile t+1), so that a tile's left neighbour was started
+// nrow items -- most of a grid-wide round -- earlier and its descriptor is normally there when looked for.
+template <int NV, int THREADS, int MINB, int UNR>
+__global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restrict__ ct, const double* __restrict__ rt,
+                                                                 i64 nrow, i64 ncol, const double* __restrict__ x0v,
+                                                                 const double* __restrict__ cst, double reps,
+                                                                 double* __restrict__ hx, double* __restrict__ hy,
+                                                                 unsigned long long* __restrict__ desc) {
+  constexpr int NM = 4 * NV, NT = 1 + 2 * NV, TW = THREADS - 1, kWarps = THREADS / 32;
+  constexpr unsigned kMask = (1u << NM) - 1u;
+  __shared__ double lamS[NM][THREADS];
+  __shared__ double phiS[NM][THREADS];
+  __shared__ unsigned shw[2 * kWarps];
+  __shared__ unsigned s_state;
   const DpConst K = dp_load(cst);
-  for (i64 r = blockIdx.x; r < nrow; r += gridDim.x) {
-    if (threadIdx.x < NT) rrow[threadIdx.x] = rt[r * NT + threadIdx.x];
-    if (threadIdx.x < NM) raw[threadIdx.x][0] = x0v[threadIdx.x];  // x_0 = lon_grid[0,0] of that mesh
-    if (threadIdx.x == 0) s_carry = 0u;
+  const i64 ntile = (ncol + TW - 1) / TW;
+  const i64 nitem = nrow * ntile;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (i64 item = blockIdx.x; item < nitem; item += gridDim.x) {
+    const i64 t = item / nrow, r = item - t * nrow;
+    const i64 c = t * TW + (i64)threadIdx.x - 1;
+    const bool virt = c < 0;
+    const bool valid = !virt && c < ncol;
+    if (valid) {
+      const Cx* cc = ct + c * NT;
+      const double* rr = rt + r * NT;
+#pragma unroll UNR
+      for (int m = 0; m < NM; ++m) {
+        const int lvl = m >> 2, kind = m & 3;
+        const double rv = rr[kind < 2 ? 0 : 2 * lvl + kind - 1];        // r at j (kinds 0,1) or j +- (lvl+1) eps
+        const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];            // e' at i +- (lvl+1) eps (kinds 0,1) or i
+        double l, p;
+        dp_vertex(rv, ep, K, l, p);
+        lamS[m][threadIdx.x] = l;
+        phiS[m][threadIdx.x] = p;
+      }
+    } else {
+#pragma unroll
+      for (int m = 0; m < NM; ++m) { lamS[m][threadIdx.x] = virt ? x0v[m] : 0.0; }
+    }
     __syncthreads();
-    for (i64 t0 = 0; t0 < ncol; t0 += kScanThreads) {
-      const i64 c = t0 + threadIdx.x;
-      const bool valid = c < ncol;
-      double lam[NM], phi[NM];
-      if (valid) {
-        const Cx* cc = ct + c * NT;
-        const Cx e0 = cc[0];
+    Map2 mp{0u, 0xffffffffu};
+    if (valid && threadIdx.x > 0) {
+      mp.f0 = 0u; mp.f1 = 0u;
 #pragma unroll
-        for (int m = 0; m < NV; ++m) {
-          dp_vertex(rrow[0], cc[1 + 2 * m], K, lam[4 * m + 0], phi[4 * m + 0]);      // (j, i+(m+1)eps)
-          dp_vertex(rrow[0], cc[2 + 2 * m], K, lam[4 * m + 1], phi[4 * m + 1]);      // (j, i-(m+1)eps)
-          dp_vertex(rrow[1 + 2 * m], e0, K, lam[4 * m + 2], phi[4 * m + 2]);         // (j+(m+1)eps, i)
-          dp_vertex(rrow[2 + 2 * m], e0, K, lam[4 * m + 3], phi[4 * m + 3]);         // (j-(m+1)eps, i)
+      for (int m = 0; m < NM; ++m) {
+        const double v = lamS[m][threadIdx.x], p = lamS[m][threadIdx.x - 1];
+        mp.f0 |= ((v - p) > 100 ? 1u : 0u) << m;
+        mp.f1 |= ((v - (p - 360)) > 100 ? 1u : 0u) << m;
+      }
+    }
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      Map2 e;
+      e.f0 = __shfl_up_sync(0xffffffffu, mp.f0, off);
+      e.f1 = __shfl_up_sync(0xffffffffu, mp.f1, off);
+      if (lane >= (unsigned)off) mp = compose(e, mp);
+    }
+    if (lane == 31u) { shw[2 * warp] = mp.f0; shw[2 * warp + 1] = mp.f1; }
+    __syncthreads();
+    if (warp > 0) {
+      Map2 pre{shw[0], shw[1]};
+      for (unsigned w = 1; w < warp; ++w) pre = compose(pre, Map2{shw[2 * w], shw[2 * w + 1]});
+      mp = compose(pre, mp);
+    }
+    if (threadIdx.x == THREADS - 1) {
+      unsigned s_in = 0u;
+      if (t > 0) {
+        desc_store(desc + item, kDescAgg | ((unsigned long long)(mp.f0 & kMask) << 16) | (mp.f1 & kMask));
+        Map2 acc{0u, 0xffffffffu};
+        for (i64 k = item - nrow;; k -= nrow) {          // tiles t-1, t-2, ... of this row: tile 0 always has a state
+          unsigned long long d;
+          do { d = desc_load(desc + k); } while ((d >> 62) == 0ull);
+          if ((d >> 62) == 2ull) { s_in = apply_map(acc, (unsigned)(d & 0xffffull)); break; }
+          acc = compose(Map2{(unsigned)((d >> 16) & 0xffffull), (unsigned)(d & 0xffffull)}, acc);
         }
-      } else {
-#pragma unroll
-        for (int m = 0; m < NM; ++m) { lam[m] = 0.0; phi[m] = 0.0; }
       }
-#pragma unroll
-      for (int m = 0; m < NM; ++m) raw[m][threadIdx.x + 1] = lam[m];
-      __syncthreads();
-      Map2 mp{0u, 0u};
-      if (valid) {
-#pragma unroll
-        for (int m = 0; m < NM; ++m) {
-          const double p = raw[m][threadIdx.x];
-          mp.f0 |= ((lam[m] - p) > 100 ? 1u : 0u) << m;
-          mp.f1 |= ((lam[m] - (p - 360)) > 100 ? 1u : 0u) << m;
-        }
-      } else {
-        mp.f0 = 0u; mp.f1 = 0xffffffffu;
+      desc_store(desc + item, kDescState | (apply_map(mp, s_in) & kMask));
+      s_state = s_in;
+    }
+    __syncthreads();
+    if (valid && threadIdx.x > 0) {
+      const unsigned st = apply_map(mp, s_state);
+#pragma unroll UNR
+      for (int q = 0; q < 2 * NV; ++q) {                                  // pair q: meshes 2q (plus) and 2q+1 (minus)
+        double l0 = lamS[2 * q][threadIdx.x], l1 = lamS[2 * q + 1][threadIdx.x];
+        if ((st >> (2 * q)) & 1u) l0 = l0 - 360;                           // :473
+        if ((st >> (2 * q + 1)) & 1u) l1 = l1 - 360;
+        phiS[2 * q][threadIdx.x] = haversine(l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
       }
-      const unsigned s_in = s_carry;
-      const unsigned st = tile_scan_states<kScanThreads>(mp, s_in, sh);
-      const i64 last = (ncol - t0 < kScanThreads ? ncol - t0 : kScanThreads) - 1;
-      if ((i64)threadIdx.x == last) {
-#pragma unroll
-        for (int m = 0; m < NM; ++m) raw[m][0] = lam[m];
-        s_carry = st;
-      }
-      if (valid) {
-#pragma unroll
-        for (int m = 0; m < NM; ++m)
-          if ((st >> m) & 1u) lam[m] = lam[m] - 360;                                 // :473
-        double dsi[3] = {0, 0, 0}, dsj[3] = {0, 0, 0};
-#pragma unroll
-        for (int m = 0; m < NV; ++m) {
-          // great_arc_distance(j, i+s, j, i-s): mesh0 = plus, mesh1 = minus (:538,:541,:544)
-          dsi[m] = haversine(lam[4 * m + 0], phi[4 * m + 0], lam[4 * m + 1], phi[4 * m + 1]);
-          dsj[m] = haversine(lam[4 * m + 2], phi[4 * m + 2], lam[4 * m + 3], phi[4 * m + 3]);
-        }
-        hx[r * ncol + c] = fd_combine<2 * NV>(dsi[0], dsi[1], dsi[2], reps);
-        hy[r * ncol + c] = fd_combine<2 * NV>(dsj[0], dsj[1], dsj[2], reps);
-      }
-      __syncthreads();
+      // pair 2m = i-direction at level m, pair 2m+1 = j-direction (:538-546, :553-561)
+      hx[r * ncol + c] = fd_combine<2 * NV>(phiS[0][threadIdx.x], NV > 1 ? phiS[4][threadIdx.x] : 0.0,
+                                            NV > 2 ? phiS[8][threadIdx.x] : 0.0, reps);
+      hy[r * ncol + c] = fd_combine<2 * NV>(phiS[2][threadIdx.x], NV > 1 ? phiS[6][threadIdx.x] : 0.0,
+                                            NV > 2 ? phiS[10][threadIdx.x] : 0.0, reps);
     }
   }
 }
@@ -1115,7 +1160,7 @@ int ogg_device_count(void) {
 
 long long ogg_launch_count(void) { return g_launches; }
 int ogg_timing_enable(int on) {
-  g_timing = on != 0;
+  g_timing = on < 0 ? 0 : (on > 2 ? 1 : on);
   return OGG_OK;
 }
 int ogg_timing_reset(void) {
@@ -1442,15 +1487,39 @@ static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow,
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
+template <typename KERN>
+static int dp_hsamples_launch(KERN kern, int threads, int* per_sm, const Cx* ct, const double* rt, i64 nrow, i64 ncol,
+                              const double* x0v, const double* cst, double reps, double* hx, double* hy, cudaStream_t st) {
+  const i64 ntile = (ncol + threads - 2) / (threads - 1);
+  const i64 nitem = nrow * ntile;
+  Scratch ws(st);
+  unsigned long long* desc;
+  OGG_CUDA(ws.get(&desc, (size_t)nitem));
+  OGG_CUDA(cudaMemsetAsync(desc, 0, (size_t)nitem * 8, st));
+  if (*per_sm == 0) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, kern, threads, 0) != cudaSuccess || *per_sm < 1) *per_sm = 1;
+  }
+  const i64 cap = (i64)num_sms() * *per_sm;
+  const unsigned g = (unsigned)(nitem < cap ? nitem : cap);
+  void* args[] = {(void*)&ct, (void*)&rt, (void*)&nrow, (void*)&ncol, (void*)&x0v, (void*)&cst, (void*)&reps,
+                  (void*)&hx, (void*)&hy, (void*)&desc};
+  launch_begin(KID_DP_HSAMPLES, st);
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(g), dim3(threads), args, 0, st);
+  launch_end(st);
+  OGG_CUDA(e);
+  return OGG_OK;
+}
+template <int NV, int THREADS, int MINB, int UNR>
+static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
+                         double reps, double* hx, double* hy, cudaStream_t st) {
+  static int per_sm = 0;   // per instantiation
+  return dp_hsamples_launch(k_dp_hsamples<NV, THREADS, MINB, UNR>, THREADS, &per_sm, ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
+}
 static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
                        double reps, double* hx, double* hy, cudaStream_t st) {
-  const i64 cap = (i64)num_sms() * 4;
-  const unsigned g = (unsigned)(nrow < cap ? nrow : cap);
-  if (nv == 1) OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<1>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
-  else if (nv == 2) OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<2>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
-  else OGG_LAUNCH(KID_DP_HSAMPLES, (k_dp_hsamples<3>), (g, kScanThreads), (st), ct, rt, nrow, ncol, x0v, cst, reps, hx, hy);
-  OGG_LAUNCH_CHECK();
-  return OGG_OK;
+  if (nv == 1) return dp_hsamples_t<1, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
+  if (nv == 2) return dp_hsamples_t<2, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
+  return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
 }
 static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
   if (nv == 1) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
