@@ -81,10 +81,13 @@ int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64
                              double lat0_bp, double lon_bp, double rp, double* h_i_inv, double* h_j_inv,
                              void* stream);
 /* bipolar_cap_metrics_quad_fast (OGG:136-188) for cell rows [j0, j1) of an nx x ny cap.
- * dxq [(j1-j0) + (j1==ny)][nx]  (the extra row is the pole row dxq[ny,:]);  dyq [j1-j0][nx+1];  daq [j1-j0][nx]. */
+ * dxq [(j1-j0) + (j1==ny)][nx]  (the extra row is the pole row dxq[ny,:]);  dyq [j1-j0][nx+1];  daq [j1-j0][nx].
+ * flags: OGG_QUAD_NO_TOP_DX_ROW leaves dxq[ny,:] unwritten (in a stitched grid that row belongs to the sub-grid above,
+ * the [:-1] of OGG:1316-1362, which may be writing it concurrently on another stream). */
+#define OGG_QUAD_NO_TOP_DX_ROW 1
 int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lat0_bp,
-                                 double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
-                                 void* stream);
+                                 double lon_bp, double rp, double Re, int flags, double* dxq, double* dyq,
+                                 double* daq, void* stream);
 
 /* ---- quadrature helpers (OGG:191-255), batched --------------------------------------------------------------- */
 /* a[n], b[n] are HOST pointers */
@@ -119,7 +122,8 @@ int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i
                     void* stream);
 /* displacedPoleCap_metrics_quad (OGG:565-601) for cell rows [j0, j1); output shapes as the bipolar twin */
 int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lon0, double lat0,
-                        double lon_dp, double r_dp, double Re, double* dxq, double* dyq, double* daq, void* stream);
+                        double lon_dp, double r_dp, double Re, int flags, double* dxq, double* dyq, double* daq,
+                        void* stream);
 
 /* ---- reductions for metrics_error (OGG:747-756) and the global-area check ------------------------------------------- */
 /* out[0] = sum_{k<n} a[k*stride]   (fixed-shape tree: deterministic for given n) */

@@ -16,6 +16,7 @@ _int = ctypes.c_int
 _vp = ctypes.c_void_p
 
 OGG_BAND_SKIP_TOP_VERTEX_ROW = 1
+OGG_QUAD_NO_TOP_DX_ROW = 1
 OGG_BAND_NO_METRICS = 2
 
 # name -> argtypes, exactly as declared in include/ogg_b200.h
@@ -31,7 +32,7 @@ SIGNATURES = {
     "ogg_bipolar_projection": [_dp, _dp, _i64, _d, _d, _int, _dp, _dp, _dp, _dp, _vp],
     "ogg_bipolar_cap_mesh": [_i64, _i64, _i64, _i64, _d, _d, _d, _dp, _dp, _dp, _dp, _vp],
     "ogg_bipolar_cap_ij_array": [_dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _dp, _dp, _vp],
-    "ogg_bipolar_cap_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _dp, _vp],
+    "ogg_bipolar_cap_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _int, _dp, _dp, _dp, _vp],
     "ogg_quad_positions": [_int, ctypes.POINTER(_d), ctypes.POINTER(_d)],
     "ogg_quad_average": [_dp, _i64, _int, _dp, _vp],
     "ogg_quad_average_2d": [_dp, _i64, _int, _dp, _vp],
@@ -42,7 +43,7 @@ SIGNATURES = {
     "ogg_dp_cap_mesh": [_i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
     "ogg_great_arc_distance": [_dp, _dp, _dp, _dp, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _vp],
     "ogg_numerical_h": [_int, _dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _vp],
-    "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _dp, _dp, _dp, _vp],
+    "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _dp, _dp, _vp],
     "ogg_sum_strided": [_dp, _i64, _i64, _dp, _vp],
     "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
     "ogg_launch_count": [], "ogg_timing_enable": [_int], "ogg_timing_reset": [], "ogg_timing_kernels": [],

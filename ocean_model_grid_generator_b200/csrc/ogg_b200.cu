@@ -1304,12 +1304,12 @@ int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64
 }
 
 int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lat0_bp, double lon_bp,
-                                 double rp, double Re, double* dxq, double* dyq, double* daq, void* stream) {
+                                 double rp, double Re, int flags, double* dxq, double* dyq, double* daq, void* stream) {
   QuadNodes q;
   if (quad_nodes_host(order, &q)) return OGG_ERR_UNCODED_ORDER;
   if (nx < 1 || ny < 1 || j0 < 0 || j1 > ny || j0 >= j1 || !dxq || !dyq || !daq) return OGG_ERR_ARG;
   cudaStream_t st = S(stream);
-  const bool top = j1 == ny;
+  const bool top = j1 == ny && !(flags & OGG_QUAD_NO_TOP_DX_ROW);
   const i64 ncr = j1 - j0;
   const i64 nuc = (order - 1) * nx + 1;
   const i64 nur = (order - 1) * ncr + 1 + (top ? 1 : 0);  // + the exact pole row
@@ -1567,7 +1567,7 @@ int ogg_numerical_h(int direction, const double* j, int64_t njl, const double* i
 }
 
 int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j1, double lon0, double lat0, double lon_dp,
-                        double r_dp, double Re, double* dxq, double* dyq, double* daq, void* stream) {
+                        double r_dp, double Re, int flags, double* dxq, double* dyq, double* daq, void* stream) {
   QuadNodes q;
   if (quad_nodes_host(order, &q)) return OGG_ERR_UNCODED_ORDER;      // quad_positions raises first (:567)
   if (order != 2 && order != 4) return OGG_ERR_ORDER_NOT_CODED;      // numerical_hi(order=order) (:583)
@@ -1596,7 +1596,7 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
   if (rc) return rc;
   for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
     const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
-    const bool top = c1 == ny;
+    const bool top = c1 == ny && !(flags & OGG_QUAD_NO_TOP_DX_ROW);
     const i64 nur = (order - 1) * (c1 - c0) + 1;                                           // closing row = row ny when top
     OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nur + 1, 256), 256), (st), q, order, c0, c1, ny, 0, jv);    // :573-576
     OGG_LAUNCH_CHECK();

@@ -111,7 +111,7 @@ def bipolar_cap_metrics_quad_fast(order, nx, ny, lat0_bp, lon_bp, rp, Re=_defaul
     nx, ny = int(nx), int(ny)
     dxq, dyq, daq = _dev.empty(ny + 1, nx), _dev.empty(ny, nx + 1), _dev.empty(ny, nx)
     _cabi.call("ogg_bipolar_cap_metrics_quad", int(order), nx, ny, 0, ny, float(lat0_bp), float(lon_bp), float(rp),
-               float(Re), _dev.ptr(dxq), _dev.ptr(dyq), _dev.ptr(daq), _dev.stream())
+               float(Re), 0, _dev.ptr(dxq), _dev.ptr(dyq), _dev.ptr(daq), _dev.stream())
     return _out(dxq, device), _out(dyq, device), _out(daq, device)
 
 
@@ -436,7 +436,7 @@ def displacedPoleCap_metrics_quad(order, nx, ny, lon0, lat0, lon_dp, r_dp, Re=_d
     nx, ny = int(nx), int(ny)
     dxq, dyq, daq = _dev.empty(ny + 1, nx), _dev.empty(ny, nx + 1), _dev.empty(ny, nx)
     _cabi.call("ogg_dp_metrics_quad", int(order), nx, ny, 0, ny, float(lon0), float(lat0), float(lon_dp), float(r_dp),
-               float(Re), _dev.ptr(dxq), _dev.ptr(dyq), _dev.ptr(daq), _dev.stream())
+               float(Re), 0, _dev.ptr(dxq), _dev.ptr(dyq), _dev.ptr(daq), _dev.stream())
     return _out(dxq, device), _out(dyq, device), _out(daq, device)
 
 

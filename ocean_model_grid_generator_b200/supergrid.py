@@ -213,6 +213,7 @@ class Supergrid(object):
         self.dx = _dev.empty(nyl + 1, nxp - 1)
         self.dy, self.area = _dev.empty(nyl, nxp), _dev.empty(nyl, nxp - 1)
         self._iv = None
+        self._streams = self._events = None
         self._lam_dev = {}
 
     # number of vertex rows that are really this rank's (the closing row belongs to the last rank only)
@@ -224,18 +225,40 @@ class Supergrid(object):
         n = self.vertex_rows
         return dict(x=self.x[:n], y=self.y[:n], dx=self.dx[:n], dy=self.dy, area=self.area, angle_dx=self.angle_dx[:n])
 
-    def build(self):
-        """Launch every piece's kernels on the current stream (asynchronous)."""
+    def build(self, concurrent=True):
+        """Launch every piece's kernels (asynchronous).  The pieces write disjoint rows, so each gets its own stream
+        forked from / joined to the current one: the caps' many small table kernels and the HBM-bound band fills
+        overlap the FP64-bound cap quadratures instead of queueing behind them.  Caps are launched first."""
+        import torch
         plan = self.plan
         if plan.skip_metrics:                                       # OGG:1009-1011 etc.: metrics stay -1
             self.dx.fill_(-1.0); self.dy.fill_(-1.0); self.area.fill_(-1.0)
-        off = 0
+        jobs, off = [], 0
         last = len(plan.pieces) - 1
         for k, (piece, (c0, c1)) in enumerate(zip(plan.pieces, self.slabs)):
             if c1 > c0:
-                closing = (k == last and self.rank == self.world - 1)
-                self._build_piece(piece, c0, c1, off, closing)
+                jobs.append((piece, c0, c1, off, k == last and self.rank == self.world - 1))
             off += c1 - c0
+        if not concurrent or len(jobs) < 2:
+            for job in jobs:
+                self._build_piece(*job)
+            return self
+        jobs.sort(key=lambda j: {"dp": 0, "bipolar": 1}.get(j[0].kind, 2))
+        main = torch.cuda.current_stream()
+        if self._streams is None:
+            self._streams = [torch.cuda.Stream() for _ in range(4)]
+            self._events = [torch.cuda.Event() for _ in range(5)]
+        fork = self._events[4]
+        fork.record(main)
+        for n, job in enumerate(jobs):
+            side = self._streams[n % 4]
+            if n < 4:
+                side.wait_event(fork)
+            with torch.cuda.stream(side):
+                self._build_piece(*job)
+        for n in range(min(len(jobs), 4)):
+            self._events[n].record(self._streams[n])
+            main.wait_event(self._events[n])
         return self
 
     def _views(self, off, nrows_v):
@@ -262,30 +285,27 @@ class Supergrid(object):
             _cabi.call("ogg_band_fill_metrics", _dev.ptr(lam), _dev.ptr_off(phi, j0), c1 - c0 + 1, nxp, Re, flags,
                        px, py, pdx, pdy, parea, pangle, st)
         elif piece.kind == "bipolar":
+            # vertex rows written: this slab's lower edges, plus its top edge only when it closes the grid -- any other
+            # top row belongs to the slab / sub-grid above, which writes it (possibly concurrently, on another stream)
             p = piece.p
             j0, j1 = piece.row0 + c0, piece.row0 + c1
-            _cabi.call("ogg_bipolar_cap_mesh", plan.Ni, p["Nj"], j0, j1 + 1, p["lat0_bp"], p["lon_bp"], p["rp"],
+            nv = c1 - c0 + (1 if closing else 0)
+            _cabi.call("ogg_bipolar_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lat0_bp"], p["lon_bp"], p["rp"],
                        px, py, None, None, st)
-            _cabi.call("ogg_angle_x", px, py, c1 - c0 + 1, nxp, pangle, st)                       # OGG:1071
+            _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                                # OGG:1071
             if not plan.skip_metrics:
                 _cabi.call("ogg_bipolar_cap_metrics_quad", 5, plan.Ni, p["Nj"], j0, j1, p["lat0_bp"], p["lon_bp"],
-                           p["rp"], Re, pdx, pdy, parea, st)                                       # OGG:1068
-                if j1 != p["Nj"]:
-                    self._dx_row_fix(piece, j1, off + (c1 - c0))
+                           p["rp"], Re, 0 if closing else _cabi.OGG_QUAD_NO_TOP_DX_ROW, pdx, pdy, parea, st)   # OGG:1068
         else:  # displaced pole
             p = piece.p
             j0, j1 = piece.row0 + c0, piece.row0 + c1
-            _cabi.call("ogg_dp_cap_mesh", plan.Ni, p["Nj"], j0, j1 + 1, p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"],
+            nv = c1 - c0 + (1 if closing else 0)
+            _cabi.call("ogg_dp_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"],
                        px, py, st)                                                                 # OGG:1162
-            _cabi.call("ogg_angle_x", px, py, c1 - c0 + 1, nxp, pangle, st)                       # OGG:1163
+            _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                                # OGG:1163
             if not plan.skip_metrics:
                 _cabi.call("ogg_dp_metrics_quad", 4, plan.Ni, p["Nj"], j0, j1, p["lon0"], p["lat0"], p["lon_dp"],
-                           p["r_dp"], Re, pdx, pdy, parea, st)                                     # OGG:1170
-
-    def _dx_row_fix(self, piece, j1, row):
-        """A slab that ends below the cap's top has no dx for its closing vertex row; it belongs to the next rank
-        (or is overwritten by the next piece), nothing to do."""
-        return
+                           p["r_dp"], Re, 0 if closing else _cabi.OGG_QUAD_NO_TOP_DX_ROW, pdx, pdy, parea, st)  # OGG:1170
 
     # ---- reductions / checks -------------------------------------------------------------------------
     def area_sum(self):

@@ -104,7 +104,7 @@ def test_bipolar_row_slabs_match_whole(G):
     for (j0, j1) in [(0, 5), (5, 6), (6, 13)]:
         top = 1 if j1 == ny else 0
         dxq, dyq, daq = D.empty(j1 - j0 + top, nx), D.empty(j1 - j0, nx + 1), D.empty(j1 - j0, nx)
-        _cabi.call("ogg_bipolar_cap_metrics_quad", 5, nx, ny, j0, j1, lat0, lon_bp, rp, 6371.0e3, D.ptr(dxq), D.ptr(dyq),
+        _cabi.call("ogg_bipolar_cap_metrics_quad", 5, nx, ny, j0, j1, lat0, lon_bp, rp, 6371.0e3, 0, D.ptr(dxq), D.ptr(dyq),
                    D.ptr(daq), D.stream())
         assert_bits(D.to_host(dxq), whole[0][j0:j1 + top], "dxq slab")
         assert_bits(D.to_host(dyq), whole[1][j0:j1], "dyq slab")
@@ -174,7 +174,7 @@ def test_dp_row_slabs_match_whole(G):
     for (j0, j1) in [(0, 4), (4, 5), (5, 11)]:
         top = 1 if j1 == ny else 0
         dxq, dyq, daq = D.empty(j1 - j0 + top, nx), D.empty(j1 - j0, nx + 1), D.empty(j1 - j0, nx)
-        _cabi.call("ogg_dp_metrics_quad", 4, nx, ny, j0, j1, *args, 6371.0e3, D.ptr(dxq), D.ptr(dyq), D.ptr(daq), D.stream())
+        _cabi.call("ogg_dp_metrics_quad", 4, nx, ny, j0, j1, *args, 6371.0e3, 0, D.ptr(dxq), D.ptr(dyq), D.ptr(daq), D.stream())
         assert_bits(D.to_host(dxq), whole[0][j0:j1 + top], "dxq slab")
         assert_bits(D.to_host(dyq), whole[1][j0:j1], "dyq slab")
         assert_bits(D.to_host(daq), whole[2][j0:j1], "daq slab")

@@ -33,10 +33,10 @@ out = {}
 
 def run():
     dx, dy, da = D.empty(Nj_bp + 1, Ni), D.empty(Nj_bp, Ni + 1), D.empty(Nj_bp, Ni)
-    _cabi.call("ogg_bipolar_cap_metrics_quad", 5, Ni, Nj_bp, Nj_bp - Nj_bp // world, Nj_bp, lat0_bp, lon0, rp, 6371.0e3, D.ptr(dx), D.ptr(dy), D.ptr(da), st)
+    _cabi.call("ogg_bipolar_cap_metrics_quad", 5, Ni, Nj_bp, Nj_bp - Nj_bp // world, Nj_bp, lat0_bp, lon0, rp, 6371.0e3, 0, D.ptr(dx), D.ptr(dy), D.ptr(da), st)
     n = Nj_sc - jmin
     sx, sy, sa = D.empty(n + 1, Ni), D.empty(n, Ni + 1), D.empty(n, Ni)
-    _cabi.call("ogg_dp_metrics_quad", 4, Ni, Nj_sc, Nj_sc - n // world, Nj_sc, lon0, -78.0, 80.0, 0.2, 6371.0e3, D.ptr(sx), D.ptr(sy), D.ptr(sa), st)
+    _cabi.call("ogg_dp_metrics_quad", 4, Ni, Nj_sc, Nj_sc - n // world, Nj_sc, lon0, -78.0, 80.0, 0.2, 6371.0e3, 0, D.ptr(sx), D.ptr(sy), D.ptr(sa), st)
     out.update(bp=(dx[:-1], dy, da), dp=(sx[:-1], sy, sa))
 
 
