@@ -43,6 +43,9 @@ def parse():
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--resolution", type=float, default=0.0, help="override inverse resolution r (default: per --gpus)")
     p.add_argument("--r_dp", type=float, default=0.2)
+    p.add_argument("--slabs", type=int, default=0,
+                   help="strong-scaling mode for grids larger than one GPU's HBM: cut the grid into V row-slabs; rank g builds "
+                        "slabs g, g+N, ... one after the other in one slab's worth of buffers (V %% N == 0)")
     p.add_argument("--no_cpu_baseline", action="store_true")
     p.add_argument("--no_e2e", action="store_true")
     return p.parse_args()
@@ -189,15 +192,26 @@ def run_ours(args):
     import io
     with contextlib.redirect_stdout(io.StringIO()):
         plan = SG.plan_supergrid(**plan_args)
-        sg = SG.Supergrid(plan, rank, world)
+    V = args.slabs if args.slabs else world
+    if V % world:
+        raise SystemExit("--slabs must be a multiple of --gpus")
+    mine = list(range(rank, V, world))
+    sg = SG.Supergrid(plan, mine[0], V, capacity_world=V if args.slabs else None)
     npoints = plan.nyp * plan.nxp
-    area_out = D.empty(1)
+    area_parts = torch.zeros(len(mine), dtype=torch.float64, device="cuda")
+    my_slabs = []
+    for v in mine:
+        my_slabs.append(list(sg.set_slab(v, V).slabs))
+    sg.set_slab(mine[0], V)
 
     def step():
-        sg.build()
-        _cabi.call("ogg_sum_strided", D.ptr(sg.area), sg.area.numel(), 1, D.ptr(area_out), D.stream())
+        for n, v in enumerate(mine):
+            if len(mine) > 1:
+                sg.set_slab(v, V)
+            sg.build()
+            _cabi.call("ogg_sum_strided", D.ptr(sg.area), sg.area.numel(), 1, D.ptr_off(area_parts, n), D.stream())
         if dist is not None:
-            dist.all_reduce(area_out)      # the single global-area all-reduce (NCCL, 8 bytes)
+            dist.all_reduce(area_parts)    # the single global-area all-reduce (NCCL, 8 bytes per slab held)
 
     def barrier():
         if dist is not None:
@@ -207,7 +221,7 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    total_area = float(area_out[0])
+    total_area = float(area_parts.sum())
     # ---- timed region: K steps, CUDA events on the launching stream, per-kernel events inside --------------
     sampler = ClockSampler(local)
     lib.ogg_timing_reset()
@@ -252,7 +266,7 @@ def run_ours(args):
 
     # ---- end to end through the public API: plan + H2D of the 1-D laws + build + D2H of the six arrays ------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and not args.slabs:
         pinned = None
         times = []
         for it in range(3):
@@ -297,19 +311,21 @@ def run_ours(args):
     lib.ogg_fp64_issue_rate(20000, ctypes.byref(rate))
     fp64_peak_tf = rate.value / 1e3
     units = {}
-    for piece, (c0, c1) in zip(plan.pieces, sg.slabs):
-        if c1 <= c0:
-            continue
-        if piece.kind == "dp":
-            units["dp_hsamples"] = (3 * (c1 - c0) + 1) * (3 * plan.Ni + 1)
-        elif piece.kind == "bipolar":
-            units["bipolar_samples"] = (4 * (c1 - c0) + 1 + (1 if piece.row0 + c1 == piece.p["Nj"] else 0)) * (4 * plan.Ni + 1)
-        else:
-            units["band_fill"] = units.get("band_fill", 0) + (c1 - c0) * plan.nxp
+    for bounds in my_slabs:
+        for piece, (c0, c1) in zip(plan.pieces, bounds):
+            if c1 <= c0:
+                continue
+            if piece.kind == "dp":
+                units["dp_hsamples"] = units.get("dp_hsamples", 0) + (3 * (c1 - c0) + 1) * (3 * plan.Ni + 1)
+            elif piece.kind == "bipolar":
+                units["bipolar_quad_fused"] = units.get("bipolar_quad_fused", 0) + \
+                    (4 * (c1 - c0) + 1 + (1 if piece.row0 + c1 == piece.p["Nj"] else 0)) * (4 * plan.Ni + 1)
+            else:
+                units["band_fill"] = units.get("band_fill", 0) + (c1 - c0) * plan.nxp
     dom = max(kern, key=lambda k: kern[k][0]) if kern else None
     roof = None
     kernels_ms = {k: round(v[0] / args.steps, 4) for k, v in sorted(kern_all.items(), key=lambda kv: -kv[1][0])}
-    if dom in ("dp_hsamples", "bipolar_samples"):
+    if dom in ("dp_hsamples", "bipolar_quad_fused"):
         ops = OPS_DP_SAMPLE if dom == "dp_hsamples" else OPS_BP_SAMPLE
         per_step_ms = kern[dom][0] / args.steps
         ach = ops * units[dom] / (per_step_ms * 1e-3) / 1e12
@@ -332,11 +348,13 @@ def run_ours(args):
                     "frac": ach / hbm_peak, "peak_source": hbm_src, "kernel_ms_per_step": per_step_ms}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.slabs else "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": "%s: full tripolar supergrid %dx%d vertices (displaced-pole cap + Southern Ocean + Mercator + "
                                    "bipolar cap), x,y,dx,dy,area,angle_dx" % (wl, plan.nyp, plan.nxp),
-                       "sharding": "latitude row-slabs of every sub-grid, %d rank(s); weak scaling: r=4/6/8/12 at N=1/2/4/8" % world,
+                       "sharding": ("latitude row-slabs of every sub-grid, %d rank(s); weak scaling: r=4/6/8/12 at N=1/2/4/8" % world)
+                       if not args.slabs else ("%d latitude row-slabs of every sub-grid, %d per rank, built one after the other in "
+                                               "one slab's buffers (strong scaling: the grid is fixed)" % (V, len(mine))),
                        "cache": "each step rewrites %.0f MB of outputs + scratch, larger than the 126 MB L2; no flush needed"
                                 % (npoints * 48 / 1e6),
                        "global_area_m2": total_area},

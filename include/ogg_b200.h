@@ -128,6 +128,10 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
 /* ---- reductions for metrics_error (OGG:747-756) and the global-area check ------------------------------------------- */
 /* out[0] = sum_{k<n} a[k*stride]   (fixed-shape tree: deterministic for given n) */
 int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, void* stream);
+/* acc[0] += sum_{k<n} splitmix64(bits of a[k]) mod 2^64 (device scalar, caller zeroes it): an order-independent
+ * checksum, additive over row-slabs -- array-level parity where the arrays are too large to copy out; stands where the
+ * reference prints chksum(x, label) (OGG:19-30, sha256 of the host array) */
+int ogg_checksum_accumulate(const double* a, int64_t n, uint64_t* acc, void* stream);
 
 /* ---- launch accounting (bench.py: gpu_launches and per-kernel CUDA-event durations) ---------------------------------- */
 /* kernels launched by this library since it was loaded */

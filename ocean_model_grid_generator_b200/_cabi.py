@@ -45,6 +45,7 @@ SIGNATURES = {
     "ogg_numerical_h": [_int, _dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _vp],
     "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _dp, _dp, _vp],
     "ogg_sum_strided": [_dp, _i64, _i64, _dp, _vp],
+    "ogg_checksum_accumulate": [_dp, _i64, _vp, _vp],
     "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
     "ogg_launch_count": [], "ogg_timing_enable": [_int], "ogg_timing_reset": [], "ogg_timing_kernels": [],
     "ogg_timing_name": [_int], "ogg_timing_get": [_int, ctypes.POINTER(_d), ctypes.POINTER(ctypes.c_longlong)],

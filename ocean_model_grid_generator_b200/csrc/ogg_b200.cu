@@ -1062,6 +1062,25 @@ __global__ void __launch_bounds__(kRedThreads) k_sum_final(const double* __restr
   if (threadIdx.x == 0) out[0] = t;
 }
 
+// Order-independent 64-bit checksum of an array's bit patterns: sum over elements of mix(bits) mod 2^64 (mix = the
+// splitmix64 finaliser).  The checksum of a grid is the sum of its row-slabs' checksums -- the array-level parity tool
+// at resolutions whose arrays are too large to copy out (the role chksum, OGG:19-30, plays in the reference).
+OGG_DI unsigned long long mix64(unsigned long long z) {
+  z += 0x9e3779b97f4a7c15ull;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(kRedThreads) k_checksum(const double* __restrict__ a, i64 n,
+                                                          unsigned long long* __restrict__ acc) {
+  unsigned long long v = 0ull;
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x)
+    v += mix64((unsigned long long)__double_as_longlong(a[e]));
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+  if ((threadIdx.x & 31u) == 0u) atomicAdd(acc, v);   // integer addition: the result does not depend on the order
+}
+
 // FP64 issue-rate probe: 8 independent chains of dependent (mul, add) pairs
 __global__ void __launch_bounds__(256) k_fp64_rate(i64 iters, double seed, double* __restrict__ sink) {
   double a[8];
@@ -1620,6 +1639,17 @@ int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, voi
   OGG_LAUNCH(KID_REDUCE, (k_sum_partial), (kRedBlocks, kRedThreads), (st), a, n, stride, partial);
   OGG_LAUNCH_CHECK();
   OGG_LAUNCH(KID_REDUCE, (k_sum_final), (1, kRedThreads), (st), partial, kRedBlocks, out);
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_checksum_accumulate(const double* a, int64_t n, uint64_t* acc, void* stream) {
+  if (!acc || n < 0 || (n > 0 && !a)) return OGG_ERR_ARG;
+  if (n == 0) return OGG_OK;
+  cudaStream_t st = S(stream);
+  const i64 want = (n + kRedThreads - 1) / kRedThreads;
+  const unsigned g = (unsigned)(want < (i64)num_sms() * 8 ? want : (i64)num_sms() * 8);
+  OGG_LAUNCH(KID_REDUCE, (k_checksum), (g, kRedThreads), (st), a, (i64)n, reinterpret_cast<unsigned long long*>(acc));
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }

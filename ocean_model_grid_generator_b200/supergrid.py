@@ -8,6 +8,7 @@ latitude row-slab of each piece (one slab per GPU).
 
 Joins follow OGG:1316-1365: x, y, dx, angle_dx = lower[:-1] + upper;  dy, area = lower + upper.
 """
+import ctypes
 import sys
 import time
 
@@ -204,17 +205,44 @@ from .slabs import slab_bounds  # noqa: E402  (contiguous split of a piece's cel
 class Supergrid(object):
     """The six arrays (device tensors) of one rank's share of the supergrid."""
 
-    def __init__(self, plan, rank=0, world=1):
-        self.plan, self.rank, self.world = plan, rank, world
-        self.slabs = [slab_bounds(p.rows - 1, rank, world) for p in plan.pieces]
-        self.rows_local = sum(c1 - c0 for c0, c1 in self.slabs)    # cell rows held here
-        nxp, nyl = plan.nxp, self.rows_local
-        self.x, self.y, self.angle_dx = _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp)
-        self.dx = _dev.empty(nyl + 1, nxp - 1)
-        self.dy, self.area = _dev.empty(nyl, nxp), _dev.empty(nyl, nxp - 1)
+    def __init__(self, plan, rank=0, world=1, capacity_world=None):
+        """capacity_world=V: allocate once for the largest of V row-slabs; `set_slab(v, V)` then re-targets the same
+        buffers at slab v (a 1/120-degree grid is 279 GB: one GPU streams it through one slab's worth of HBM)."""
+        self.plan = plan
         self._iv = None
         self._streams = self._events = None
         self._lam_dev = {}
+        cap = None
+        if capacity_world is not None:
+            cap = max(sum(slab_bounds(p.rows - 1, v, capacity_world)[1] - slab_bounds(p.rows - 1, v, capacity_world)[0]
+                          for p in plan.pieces) for v in range(capacity_world))
+        self._set_bounds(rank, world)
+        nxp, nyl = plan.nxp, (self.rows_local if cap is None else cap)
+        self._cap = nyl
+        self._x, self._y, self._angle = _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp), _dev.empty(nyl + 1, nxp)
+        self._dx = _dev.empty(nyl + 1, nxp - 1)
+        self._dy, self._area = _dev.empty(nyl, nxp), _dev.empty(nyl, nxp - 1)
+
+    def _set_bounds(self, rank, world):
+        self.rank, self.world = rank, world
+        self.slabs = [slab_bounds(p.rows - 1, rank, world) for p in self.plan.pieces]
+        self.rows_local = sum(c1 - c0 for c0, c1 in self.slabs)    # cell rows held here
+
+    def set_slab(self, rank, world):
+        """Re-target the (already allocated) buffers at slab `rank` of `world`; the previous contents are overwritten
+        by the next build()."""
+        self._set_bounds(rank, world)
+        if self.rows_local > self._cap:
+            raise Exception("slab %d of %d needs %d cell rows, buffers hold %d" % (rank, world, self.rows_local, self._cap))
+        return self
+
+    # the six arrays, trimmed to the rows of the current slab (views of the capacity buffers)
+    x = property(lambda self: self._x[:self.rows_local + 1])
+    y = property(lambda self: self._y[:self.rows_local + 1])
+    angle_dx = property(lambda self: self._angle[:self.rows_local + 1])
+    dx = property(lambda self: self._dx[:self.rows_local + 1])
+    dy = property(lambda self: self._dy[:self.rows_local])
+    area = property(lambda self: self._area[:self.rows_local])
 
     # number of vertex rows that are really this rank's (the closing row belongs to the last rank only)
     @property
@@ -224,6 +252,18 @@ class Supergrid(object):
     def arrays(self):
         n = self.vertex_rows
         return dict(x=self.x[:n], y=self.y[:n], dx=self.dx[:n], dy=self.dy, area=self.area, angle_dx=self.angle_dx[:n])
+
+    def checksums(self, acc=None):
+        """Adds this slab's per-array 64-bit checksums (ogg_checksum_accumulate) to `acc` (uint64[6] device tensor, order of
+        FIELDS); the sum over all slabs equals the whole grid's checksums."""
+        import torch
+        if acc is None:
+            acc = torch.zeros(6, dtype=torch.int64, device="cuda")
+        st = _dev.stream()
+        for k, name in enumerate(FIELDS):
+            t = self.arrays()[name]
+            _cabi.call("ogg_checksum_accumulate", _dev.ptr(t), t.numel(), ctypes.c_void_p(acc.data_ptr() + 8 * k), st)
+        return acc
 
     def build(self, concurrent=True):
         """Launch every piece's kernels (asynchronous).  The pieces write disjoint rows, so each gets its own stream

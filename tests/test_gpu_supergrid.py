@@ -133,3 +133,93 @@ def test_eighth_degree_slabs_checksum(SG):
         if k in ("x", "y", "dx", "angle_dx"):
             rows.append(hosts[world - 1][k][-1:])
         assert sha(np.concatenate(rows, axis=0)) == sha(whole[k]), k
+
+
+# ---- device checksums and the slab sequence (grids larger than one GPU's HBM) -------------------------------------
+def _mix64_host(a):
+    z = np.ascontiguousarray(a, dtype=np.float64).view(np.uint64).ravel().copy()
+    with np.errstate(over="ignore"):
+        z += np.uint64(0x9e3779b97f4a7c15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xbf58476d1ce4e5b9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94d049bb133111eb)
+        z = z ^ (z >> np.uint64(31))
+        return int(z.sum(dtype=np.uint64))
+
+
+def _u64(t):
+    return [int(v) & 0xffffffffffffffff for v in t.cpu().tolist()]
+
+
+def test_checksum_kernel_matches_host(SG):
+    """ogg_checksum_accumulate == the same splitmix64 sum computed with numpy integers, and it accumulates."""
+    import ctypes
+    import torch
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    rng = np.random.default_rng(7)
+    a = rng.standard_normal(100003)
+    a[:5] = [0.0, -0.0, np.inf, np.nan, 5e-324]
+    t = D.to_dev(a)
+    acc = torch.zeros(1, dtype=torch.int64, device="cuda")
+    _cabi.call("ogg_checksum_accumulate", D.ptr(t), t.numel(), ctypes.c_void_p(acc.data_ptr()), D.stream())
+    assert _u64(acc)[0] == _mix64_host(a)
+    _cabi.call("ogg_checksum_accumulate", D.ptr(t), 17, ctypes.c_void_p(acc.data_ptr()), D.stream())
+    assert _u64(acc)[0] == (_mix64_host(a) + _mix64_host(a[:17])) % 2 ** 64
+    _cabi.call("ogg_checksum_accumulate", None, 0, ctypes.c_void_p(acc.data_ptr()), D.stream())   # empty input: no-op
+
+
+@pytest.mark.parametrize("flags,V", [("-r 2 --r_dp 0.2", 3), ("-r 8 --r_dp 0.2", 8)])
+def test_slab_sequence_in_shared_buffers(SG, flags, V):
+    """V row-slabs built one after the other in ONE slab's buffers (how one GPU streams a grid larger than its HBM):
+    the per-array checksums add up to the whole grid's, which equal the host-side checksum of the copied-out arrays."""
+    import torch
+    plan = SG.plan_supergrid(**_plan_args(_args(flags)))
+    whole = SG.build_supergrid(plan)
+    ref = _u64(whole.checksums())
+    host = whole.to_host()
+    assert ref == [_mix64_host(host[k]) for k in SG.FIELDS]
+    sg = SG.Supergrid(plan, 0, V, capacity_world=V)
+    acc = torch.zeros(6, dtype=torch.int64, device="cuda")
+    area = 0.0
+    for v in range(V):
+        sg.set_slab(v, V).build()
+        sg.checksums(acc)
+        area += sg.area_sum()
+    assert _u64(acc) == ref
+    tot = host["area"].sum()
+    assert abs(area - tot) <= 1e-12 * tot
+
+
+def test_thirtieth_degree_slabs_and_area(SG):
+    """BASELINE configs[3] (1/30 degree, OM5-class, 16821 x 21601 vertices = 17.4 GB): whole grid on one GPU == 8 row-slabs
+    (checksum of checksums, all six arrays), sphere area north of the displaced-pole cap exact to 1e-12 relative,
+    latitude strictly increasing along the symmetry meridian, equator on an odd row (OGG:1366-1370, 1425-1436)."""
+    import torch
+    from ocean_model_grid_generator_b200 import device as D
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 30 --r_dp 0.2 --ensure_nj_even")))
+    assert (plan.nyp, plan.nxp) == (16821, 21601)
+    whole = SG.build_supergrid(plan)
+    ref = _u64(whole.checksums())
+    total_area = whole.area_sum()
+    a = whole.arrays()
+    ycol = D.to_host(a["y"][:, plan.Ni // 4])
+    assert (np.diff(ycol) > 0).all() and np.searchsorted(ycol, 0.0) % 2 == 1
+    assert bool(torch.isfinite(a["area"]).all()) and float(a["area"].min()) > 0 and float(a["dx"].min()) > 0
+    assert float(a["angle_dx"].min()) >= -90.0 and float(a["angle_dx"].max()) <= 90.0
+    Re = 6371.0e3
+    j78 = plan.pieces[0].rows - 1                    # first cell row of the Southern Ocean band (78S)
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    north = G.device_sum(a["area"][j78:])
+    exact = 2 * np.pi * Re * Re * (1 - np.sin(np.deg2rad(-78.0)))
+    assert abs(north - exact) / exact < 5e-11, (north, exact)
+    del a, whole
+    torch.cuda.empty_cache()
+    V = 8
+    sg = SG.Supergrid(plan, 0, V, capacity_world=V)
+    acc = torch.zeros(6, dtype=torch.int64, device="cuda")
+    area = 0.0
+    for v in range(V):
+        sg.set_slab(v, V).build()
+        sg.checksums(acc)
+        area += sg.area_sum()
+    assert _u64(acc) == ref
+    assert abs(area - total_area) <= 1e-12 * total_area
