@@ -265,10 +265,14 @@ class Supergrid(object):
             _cabi.call("ogg_checksum_accumulate", _dev.ptr(t), t.numel(), ctypes.c_void_p(acc.data_ptr() + 8 * k), st)
         return acc
 
-    def build(self, concurrent=True):
+    def build(self, concurrent=True, host=None):
         """Launch every piece's kernels (asynchronous).  The pieces write disjoint rows, so each gets its own stream
         forked from / joined to the current one: the caps' many small table kernels and the HBM-bound band fills
-        overlap the FP64-bound cap quadratures instead of queueing behind them.  Caps are launched first."""
+        overlap the FP64-bound cap quadratures instead of queueing behind them.
+
+        host: dict of six pinned host tensors shaped like arrays(); each piece's rows are then copied out on the piece's
+        own stream as soon as its kernels are queued, bands first, so that the device->host traffic of the bands (most
+        of the bytes) runs under the caps' quadrature.  Synchronise the current stream before reading `host`."""
         import torch
         plan = self.plan
         if plan.skip_metrics:                                       # OGG:1009-1011 etc.: metrics stay -1
@@ -282,8 +286,13 @@ class Supergrid(object):
         if not concurrent or len(jobs) < 2:
             for job in jobs:
                 self._build_piece(*job)
+                if host is not None:
+                    self._copy_piece_out(host, *job)
             return self
-        jobs.sort(key=lambda j: {"dp": 0, "bipolar": 1}.get(j[0].kind, 2))
+        if host is None:   # caps first: their long kernels should not wait behind the bands
+            jobs.sort(key=lambda j: {"dp": 0, "bipolar": 1}.get(j[0].kind, 2))
+        else:              # bands first: their rows start crossing PCIe while the caps compute
+            jobs.sort(key=lambda j: {"dp": 1, "bipolar": 2}.get(j[0].kind, 0))
         main = torch.cuda.current_stream()
         if self._streams is None:
             self._streams = [torch.cuda.Stream() for _ in range(4)]
@@ -296,10 +305,23 @@ class Supergrid(object):
                 side.wait_event(fork)
             with torch.cuda.stream(side):
                 self._build_piece(*job)
+                if host is not None:
+                    self._copy_piece_out(host, *job)
         for n in range(min(len(jobs), 4)):
             self._events[n].record(self._streams[n])
             main.wait_event(self._events[n])
         return self
+
+    def _copy_piece_out(self, host, piece, c0, c1, off, closing):
+        nv, nc = c1 - c0 + (1 if closing else 0), c1 - c0
+        for name, dev, n in (("x", self._x, nv), ("y", self._y, nv), ("dx", self._dx, nv), ("angle_dx", self._angle, nv),
+                             ("dy", self._dy, nc), ("area", self._area, nc)):
+            host[name][off:off + n].copy_(dev[off:off + n], non_blocking=True)
+
+    def pinned_like(self):
+        """Six pinned host tensors shaped like arrays() (allocate once, reuse across builds)."""
+        import torch
+        return {k: torch.empty(tuple(v.shape), dtype=torch.float64, pin_memory=True) for k, v in self.arrays().items()}
 
     def _views(self, off, nrows_v):
         nxp = self.plan.nxp
@@ -359,11 +381,12 @@ def build_supergrid(plan, rank=0, world=1):
     return Supergrid(plan, rank, world).build()
 
 
-def generate(**kwargs):
-    """Public one-call API: plan + build on this GPU; returns (plan, Supergrid) with arrays resident in HBM."""
+def generate(host=None, **kwargs):
+    """Public one-call API: plan + build on this GPU; returns (plan, Supergrid) with arrays resident in HBM.
+    host: pinned tensors from Supergrid.pinned_like() to receive the six arrays (copies overlap the build)."""
     _dev.ready()
     plan = plan_supergrid(**kwargs)
-    return plan, build_supergrid(plan)
+    return plan, Supergrid(plan).build(host=host)
 
 
 # --------------------------------------------------------------------------------------------------

@@ -195,3 +195,16 @@ def test_oracle_supergrid_matches_reference_hashes(oracle, golden_configs, name,
     for k, v in golden_configs[name]["arrays"].items():
         assert list(got[k].shape) == v["shape"], (k, got[k].shape, v["shape"])
         assert sha(got[k]) == v["sha256"], (name, k)
+
+
+def test_sqrt_of_square_identity():
+    """sqrt(fl(t*t)) == |t| for binary64 round-to-nearest whenever t*t stays normal: the band kernel writes Re*|tt| for the
+    reference's Re*sqrt(0 + tt*tt) (OGG:698 with dy_i = 0 on a band)."""
+    import numpy as np
+    rng = np.random.default_rng(11)
+    mant = rng.uniform(1.0, 2.0, 10_000_000)
+    expo = rng.integers(-480, 480, mant.size)
+    t = np.ldexp(mant, expo) * rng.choice([-1.0, 1.0], mant.size)
+    edge = np.array([1.0, 1.5, np.nextafter(2.0, 0), np.nextafter(1.0, 2), 2.0 ** -499, 2.0 ** 499, np.sqrt(2.0), 3.0, 1e-3, 7e-17])
+    for v in (t, edge, np.nextafter(edge, 0), np.nextafter(edge, np.inf)):
+        assert (np.sqrt(0.0 + v * v) == np.abs(v)).all()
