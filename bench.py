@@ -269,8 +269,9 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e and not args.slabs:
         pinned = None
+        area_e2e = D.empty(1)
         times = []
-        for it in range(3):
+        for it in range(4):
             torch.cuda.synchronize()
             if dist is not None:
                 dist.barrier()
@@ -281,18 +282,23 @@ def run_ours(args):
             if pinned is None:
                 pinned = s2.pinned_like()
             s2.build(host=pinned)        # every piece's rows are copied out on its own stream while the caps compute
+            # the step's results read on the host: the six arrays (above) and the global-area check (device tree sum,
+            # 8 bytes).  No host-side parallel reduction here: an OpenMP pool left spinning after torch's CPU sum
+            # slowed the NEXT iteration's launches and PCIe copies by 60% on the 16-core box.
+            _cabi.call("ogg_sum_strided", D.ptr(s2.area), s2.area.numel(), 1, D.ptr(area_e2e), D.stream())
+            checksum = float(area_e2e[0])                # synchronises the stream: all copies have landed
             torch.cuda.synchronize()
-            checksum = float(pinned["area"].sum())      # the step's result read on the host
+            corner = float(pinned["area"][-1, -1]) if pinned["area"].numel() else 0.0
             if dist is not None:
                 dist.barrier()
             times.append(time.perf_counter() - t0)
         te = torch.tensor([min(times[1:])], dtype=torch.float64, device="cuda")
         if dist is not None:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        d2h = sum(v.numel() * 8 for v in pinned.values())
+        d2h = sum(v.numel() * 8 for v in pinned.values()) + 8
         h2d = sum(8 * (len(pc.p["lam"]) + len(pc.p["phi"])) for pc in plan.pieces if pc.kind == "band") + 8 * (plan.Ni + 1) + 4096
         e2e = {"value": npoints / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "ms": float(te[0]) * 1e3, "checksum_area_local": checksum}
+               "ms": float(te[0]) * 1e3, "checksum_area_local": checksum, "host_area_last_cell": corner}
 
     if rank != 0:
         if dist is not None:
