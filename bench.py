@@ -67,11 +67,14 @@ class ClockSampler(object):
     def __init__(self, index):
         self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
 
-    def _run_nvml(self):
-        """Fast path: NVML samples every ~2 ms, so that even a 30 ms timed region gets several clock samples."""
+    def _init_nvml(self):
         import pynvml as N
         N.nvmlInit()
-        h = N.nvmlDeviceGetHandleByIndex(self.index)
+        self._nvml = (N, N.nvmlDeviceGetHandleByIndex(self.index))
+
+    def _run_nvml(self):
+        """Fast path: NVML samples every ~2 ms, so that even a 30 ms timed region gets several clock samples."""
+        N, h = self._nvml
         mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
         bits = (("hw_slowdown", N.nvmlClocksThrottleReasonHwSlowdown),
                 ("hw_thermal_slowdown", N.nvmlClocksThrottleReasonHwThermalSlowdown),
@@ -85,8 +88,9 @@ class ClockSampler(object):
 
     def _run(self):
         try:
-            self._run_nvml()
-            return
+            if self._nvml is not None:
+                self._run_nvml()
+                return
         except Exception:
             pass
         while not self._stop.is_set():
@@ -99,6 +103,10 @@ class ClockSampler(object):
             self._stop.wait(0.05)
 
     def start(self):
+        try:
+            self._init_nvml()      # before the timed region: library load + handle lookup take tens of ms
+        except Exception:
+            self._nvml = None
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
 
@@ -377,6 +385,16 @@ def run_ours(args):
 
 
 if __name__ == "__main__":
+    # exactly ONE line on stdout: libraries that print there (NCCL's version banner) are sent to stderr
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    _print = print
+
+    def print(*args, **kw):  # noqa: A001  (only the JSON lines below call it)
+        kw.setdefault("file", _real_stdout)
+        kw.setdefault("flush", True)
+        _print(*args, **kw)
+
     a = parse()
     if a.impl == "reference":
         run_reference(a)
