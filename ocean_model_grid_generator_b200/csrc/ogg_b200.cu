@@ -625,7 +625,7 @@ __global__ void __launch_bounds__(256) k_bp_quad_tables(QuadNodes q, int n, i64 
 // h_i_inv, h_j_inv (:130-132) go to shared memory, columns stored residue-major (column c at
 // (c mod (N-1))*(TC+1) + c/(N-1)) so that phase 2 -- one thread per cell, sums in the reference's order
 // (:180-187) -- reads consecutive words across a warp.  Samples on tile edges are recomputed by the neighbour
-// (3.9 % more samples at TR=8, TC=32) instead of travelling through HBM (16 B written + 16 B read per sample).
+// (5.0 % more samples at TR=6, TC=32) instead of travelling through HBM (16 B written + 16 B read per sample).
 template <int N, int TR, int TC>
 __global__ void __launch_bounds__(256) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt, i64 nuc,
                                                        i64 ncr, i64 nx, i64 ny, double lat0_bp, double lon_bp, double rp,
@@ -902,6 +902,12 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
   }
 }
 
+// out-of-line copy for k_dp_hsamples: with the haversine inlined four times next to four inlined projections the
+// kernel's loop body overflowed the instruction cache (stalled_no_instruction 2.1 per issue); one shared copy is 4.5 %
+// faster.  Same instructions, same results.
+__device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
+  return haversine(lam0, phi0, lam1, phi1);
+}
 // --- fused numerical_hi + numerical_hj on a lattice of unique samples (OGG:583-584) ------------------------------
 // For finite-difference order 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column),
 // each needing its own longitude unwrap along the row: their 2-state maps are packed into one word and scanned
@@ -1015,7 +1021,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         double l0 = lamS[2 * q][threadIdx.x], l1 = lamS[2 * q + 1][threadIdx.x];
         if ((st >> (2 * q)) & 1u) l0 = l0 - 360;                           // :473
         if ((st >> (2 * q + 1)) & 1u) l1 = l1 - 360;
-        phiS[2 * q][threadIdx.x] = haversine(l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
+        phiS[2 * q][threadIdx.x] = haversine_ol(l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
       }
       // pair 2m = i-direction at level m, pair 2m+1 = j-direction (:538-546, :553-561)
       hx[r * ncol + c] = fd_combine<2 * NV>(phiS[0][threadIdx.x], NV > 1 ? phiS[4][threadIdx.x] : 0.0,
@@ -1140,7 +1146,7 @@ static int run_quad_cells(int order, const double* sx, const double* sy, i64 nuc
                      nuc, ncr, nx, top_row, Re, dxq, dyq, daq);
 }
 
-constexpr int kBpTileRows = 8, kBpTileCols = 32;
+constexpr int kBpTileRows = 6, kBpTileCols = 32;  // 53 KB of samples per CTA: 4 CTAs/SM (8x32: 3 CTAs/SM, 3.6 % slower)
 template <int N>
 static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
                                 double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
