@@ -271,3 +271,38 @@ def test_device_sum(G):
     a = rng.uniform(0, 1, (301, 77))
     assert abs(G.device_sum(a) - a.sum()) <= 1e-12 * a.sum()
     assert abs(G.device_sum(a, n=301, stride=77, offset=5) - a[:, 5].sum()) <= 1e-12 * a[:, 5].sum()
+
+
+# ---- smallest shapes and the row-ownership flag ---------------------------------------------------------------------
+@pytest.mark.parametrize("nx,ny", [(1, 1), (2, 1), (1, 3), (33, 1), (255, 2), (256, 2)])
+def test_smallest_caps_vs_oracle(G, oracle, nx, ny):
+    """One-cell caps, a single cell row, and column counts straddling the 255-column tile of the look-back kernel."""
+    lat0, lon_bp = 64.05895973, -300.0
+    rp = G.bipolar_rp(lat0)
+    for g, r, n in zip(G.bipolar_cap_metrics_quad_fast(5, nx, ny, lat0, lon_bp, rp),
+                       oracle.bipolar_cap_metrics_quad_fast(5, nx, ny, lat0, lon_bp, rp), ("dxq", "dyq", "daq")):
+        assert_bits(g, r, "bipolar %dx%d %s" % (nx, ny, n))
+    for g, r, n in zip(G.displacedPoleCap_metrics_quad(4, nx, ny, -300.0, -78.0, 80.0, 0.2),
+                       oracle.displacedPoleCap_metrics_quad(4, nx, ny, -300.0, -78.0, 80.0, 0.2), ("dxq", "dyq", "daq")):
+        assert_bits(g, r, "displaced pole %dx%d %s" % (nx, ny, n))
+    for g, r, n in zip(G.generate_displaced_pole_grid(nx, ny, -300.0, -78.0, 80.0, 0.2)[:2],
+                       oracle.generate_displaced_pole_grid(nx, ny, -300.0, -78.0, 80.0, 0.2)[:2], "xy"):
+        assert_bits(g, r, "dp mesh %dx%d %s" % (nx, ny, n))
+
+
+def test_quad_top_row_flag_leaves_row_untouched(G):
+    """OGG_QUAD_NO_TOP_DX_ROW: the dx row at the cap's top edge belongs to the sub-grid above (OGG:1316-1362 `[:-1]`)."""
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    nx, ny = 40, 5
+    lat0, lon_bp = 64.05895973, -300.0
+    rp = G.bipolar_rp(lat0)
+    for name, args in (("ogg_bipolar_cap_metrics_quad", (5, nx, ny, 0, ny, lat0, lon_bp, rp)),
+                       ("ogg_dp_metrics_quad", (4, nx, ny, 0, ny, -300.0, -78.0, 80.0, 0.2))):
+        ref = [D.full((ny + 1, nx), -7.0), D.empty(ny, nx + 1), D.empty(ny, nx)]
+        _cabi.call(name, *args, 6371.0e3, 0, D.ptr(ref[0]), D.ptr(ref[1]), D.ptr(ref[2]), D.stream())
+        got = [D.full((ny + 1, nx), -7.0), D.empty(ny, nx + 1), D.empty(ny, nx)]
+        _cabi.call(name, *args, 6371.0e3, _cabi.OGG_QUAD_NO_TOP_DX_ROW, D.ptr(got[0]), D.ptr(got[1]), D.ptr(got[2]), D.stream())
+        assert bool((got[0][ny] == -7.0).all()) and not bool((ref[0][ny] == -7.0).any())
+        assert_bits(D.to_host(got[0][:ny]), D.to_host(ref[0][:ny]), name + " dx")
+        assert_bits(D.to_host(got[1]), D.to_host(ref[1]), name + " dy")
+        assert_bits(D.to_host(got[2]), D.to_host(ref[2]), name + " area")

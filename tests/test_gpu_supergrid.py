@@ -223,3 +223,17 @@ def test_thirtieth_degree_slabs_and_area(SG):
         area += sg.area_sum()
     assert _u64(acc) == ref
     assert abs(area - total_area) <= 1e-12 * total_area
+
+
+@pytest.mark.parametrize("r", [6, 8])
+def test_eighth_degree_equals_cpu_oracle(SG, oracle, r):
+    """BASELINE configs[2] (1/8 degree, 4485 x 5761) and the 2-GPU weak-scaling grid (1/6 degree): every one of the six
+    arrays bit-identical to the CPU oracle's composition of the same grid (oracle/supergrid_cpu.py; ~10 s of host time)."""
+    import supergrid_cpu
+    plan = SG.plan_supergrid(**_plan_args(_args("-r %d --r_dp 0.2" % r)))
+    got = SG.build_supergrid(plan).to_host()
+    ref = supergrid_cpu.build_cpu(r, r_dp=0.2)
+    for k in NAMES:
+        assert_bits(got[k], ref[k], "r=%d %s" % (r, k))
+    tot = ref["area"].sum()
+    assert abs(got["area"].sum() - tot) <= 1e-12 * tot
