@@ -150,6 +150,15 @@ int ogg_timing_get(int id, double* ms_total, long long* launches);
  * achieved 1e9 instructions/s.  Synchronous. */
 int ogg_fp64_issue_rate(int64_t iters, double* ginstr_per_s_host);
 
+/* ---- self-test: the branch-free division / square-root sequences of the cap kernels (MathFast, csrc/ogg_trig.cuh) ------- */
+/* n pseudo-random operand sets (seed, mode 0 random / 1 raw bit patterns / 2 near-boundary significands / 3 small integers):
+ * counts3_host[0] = results accepted by the operand guards, [1] = accepted results that differ in any bit from the
+ * compiler's IEEE-754 div.rn / sqrt.rn (must be 0), [2] = in-range operand sets a guard rejected (must be 0; mode 1
+ * has no in-range promise).  mode 4: tan, arctan, arctan2, arcsin, arccos evaluated with those sequences against the
+ * same functions with the compiler's operations ([0] accepted, [1] differing).  No reference counterpart: the reference's `/` and numpy.sqrt are IEEE operations, which
+ * is what this verifies.  Synchronous. */
+int ogg_selftest_divsqrt(int64_t n, uint64_t seed, int mode, uint64_t* counts3_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -387,16 +387,17 @@ OGG_DI BpCol bp_col(double lamg, double lon_bp) {
   o.dl = lamg - lon_bp;
   return o;
 }
-template <bool FULL>
-OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, double& lams, double& phis,
-                      double& h_i_inv, double& h_j_inv) {
+// M: division / square-root policy (ogg_trig.cuh); with MathFast the caller must redo the sample if !m.ok()
+template <bool FULL, class M>
+OGG_DI void bp_sample(M& m, const typename M::Divisor& pi180, const BpRow& R, const BpCol& C, double lon_bp, double rp,
+                      double& lams, double& phis, double& h_i_inv, double& h_j_inv) {
   const double alpha2 = C.alpha2, beta2_inv = R.beta2_inv;
-  const double rden = 1.0 / (1.0 + alpha2 * beta2_inv);  // :47
+  const double rden = m.div_num_ok(1.0, 1.0 + alpha2 * beta2_inv);  // :47
   const bool huge = fabs(beta2_inv) > kHuge;
   if (FULL) {
-    double B = C.sinla * sqrt(rden);                     // :50
+    double B = C.sinla * m.sqrt_(rden);                  // :50
     if (huge) B = 0.0;                                   // :52
-    double lamc = p_asin(B) / kPi180;                    // :53
+    double lamc = m.div_by(p_asin(m, B), pi180);         // :53
     const double dl = C.dl;
     if (dl > 90 && dl <= 180) lamc = 180 - lamc;         // :58
     if (dl > 180 && dl <= 270) lamc = 180 + lamc;        // :59
@@ -406,11 +407,11 @@ OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, 
     lams = lamc + lon_bp;                                // :64
   }
   const double A = C.sinla * R.sphig;                    // :68
-  const double chic = p_acos(A);                         // :69
-  const double tc = p_tan(chic / 2);
+  const double chic = p_acos(m, A);                      // :69
+  const double tc = p_tan(m, chic / 2);
   const double q = rp * tc;
-  phis = 90 - ((2 * p_atan(q)) / kPi180);                // :70
-  const double rden2 = 1.0 / (1 + q * q);                // :72
+  phis = 90 - m.div_by(2 * p_atan(m, q), pi180);         // :70
+  const double rden2 = m.div_num_ok(1.0, 1 + q * q);     // :72
   const double M_inv = (rp * (1 + tc * tc)) * rden2;     // :73
   const double cp = p_cos(phis * kPi180);
   const double cos2phis = cp * cp;                       // :79
@@ -418,10 +419,16 @@ OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, 
   double hj = ((((cos2phis * alpha2) * (1 - alpha2)) * beta2_inv) * (1 + beta2_inv)) * r2 +
               (MM * (1 - alpha2)) * rden;                // :81-84
   if (huge) hj = MM;                                     // :86
-  h_j_inv = sqrt(hj) * R.N_inv;                          // :87
+  h_j_inv = m.sqrt_(hj) * R.N_inv;                       // :87
   double hi = (cos2phis * (1 + beta2_inv)) * r2 + ((MM * alpha2) * beta2_inv) * rden;  // :89-92
   if (huge) hi = MM;                                     // :94
-  h_i_inv = sqrt(hi);                                    // :95
+  h_i_inv = m.sqrt_(hi);                                 // :95
+}
+template <bool FULL>
+OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, double& lams, double& phis,
+                      double& h_i_inv, double& h_j_inv) {
+  MathIeee m;
+  bp_sample<FULL>(m, m.divisor(kPi180), R, C, lon_bp, rp, lams, phis, h_i_inv, h_j_inv);
 }
 
 __global__ void __launch_bounds__(256) k_bp_projection(const double* __restrict__ lamg, const double* __restrict__ phig,
@@ -626,8 +633,20 @@ __global__ void __launch_bounds__(256) k_bp_quad_tables(QuadNodes q, int n, i64 
 // (c mod (N-1))*(TC+1) + c/(N-1)) so that phase 2 -- one thread per cell, sums in the reference's order
 // (:180-187) -- reads consecutive words across a warp.  Samples on tile edges are recomputed by the neighbour
 // (5.0 % more samples at TR=6, TC=32) instead of travelling through HBM (16 B written + 16 B read per sample).
+// the same scaled sample with the compiler's division and square root: taken when an operand leaves MathFast's range
+#ifndef OGG_BP_MINB
+#define OGG_BP_MINB 4
+#endif
+struct HiHj { double a, b; };
+__device__ __noinline__ HiHj bp_qsample_ieee(BpRow R, BpCol C, double lon_bp, double rp, double lat0_bp, double dnx,
+                                             double dny) {
+  double l, p, a, b;
+  bp_sample<false>(R, C, lon_bp, rp, l, p, a, b);
+  return HiHj{((a * 2) * kPi) / dnx,                                              // :131
+              ((b * (90 - lat0_bp)) * kPi180) / dny};                             // :132
+}
 template <int N, int TR, int TC>
-__global__ void __launch_bounds__(256) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt, i64 nuc,
+__global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt, i64 nuc,
                                                        i64 ncr, i64 nx, i64 ny, double lat0_bp, double lon_bp, double rp,
                                                        double Re, double* __restrict__ dxq, double* __restrict__ dyq,
                                                        double* __restrict__ daq) {
@@ -637,15 +656,22 @@ __global__ void __launch_bounds__(256) k_bp_quad_fused(const BpCol* __restrict__
   double* sy = smem + SR * SCP;
   const i64 gr0 = (i64)blockIdx.y * TR * (N - 1), gc0 = (i64)blockIdx.x * TC * (N - 1);
   const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
+  MathFast mf;
+  const MathFast::Divisor pi180 = mf.divisor(kPi180), dnx = mf.divisor((double)nx), dny = mf.divisor((double)ny);
   for (int s = threadIdx.x; s < SR * SC; s += 256) {
     const int r = s / SC, c = s - r * SC;
     const i64 gr = gr0 + r, gc = gc0 + c;
     double a = 0.0, b = 0.0;
     if (gr < nreg && gc < nuc) {
       double l, p;
-      bp_sample<false>(rt[gr], ct[gc], lon_bp, rp, l, p, a, b);
-      a = ((a * 2) * kPi) / (double)nx;                                           // :131
-      b = ((b * (90 - lat0_bp)) * kPi180) / (double)ny;                           // :132
+      mf.reset();
+      bp_sample<false>(mf, pi180, rt[gr], ct[gc], lon_bp, rp, l, p, a, b);
+      a = mf.div_by((a * 2) * kPi, dnx);                                          // :131
+      b = mf.div_by((b * (90 - lat0_bp)) * kPi180, dny);                          // :132
+      if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, the lon_bp meridian)
+        const HiHj o = bp_qsample_ieee(rt[gr], ct[gc], lon_bp, rp, lat0_bp, (double)nx, (double)ny);
+        a = o.a; b = o.b;
+      }
     }
     const int pos = r * SCP + (c % (N - 1)) * (TC + 1) + c / (N - 1);
     sx[pos] = a;
@@ -716,23 +742,26 @@ __global__ void __launch_bounds__(128) k_quad_avg2d(const double* __restrict__ y
 // ------------------------------------------------------------------------------------------------
 struct Cx { double re, im; };
 OGG_DI Cx cmul(Cx a, Cx b) { return Cx{a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }  // numpy, strict
-OGG_DI Cx cdivn(Cx a, Cx b) {  // numpy CDOUBLE_divide (Smith)
+template <class M>
+OGG_DI Cx cdivn(M& m, Cx a, Cx b) {  // numpy CDOUBLE_divide (Smith)
   const double abr = fabs(b.re), abi = fabs(b.im);
   Cx r;
   if (abr >= abi) {
-    if (abr == 0 && abi == 0) { r.re = a.re / abr; r.im = a.im / abr; return r; }
-    const double rat = b.im / b.re;
-    const double scl = 1.0 / (b.re + b.im * rat);
+    // (0,0) divisor: numpy's inf/nan rule; under MathFast a zero b.re fails the guard of the first division instead
+    if (!M::kFast && abr == 0 && abi == 0) { r.re = a.re / abr; r.im = a.im / abr; return r; }
+    const double rat = m.div(b.im, b.re);
+    const double scl = m.div_num_ok(1.0, b.re + b.im * rat);
     r.re = (a.re + a.im * rat) * scl;
     r.im = (a.im - a.re * rat) * scl;
   } else {
-    const double rat = b.re / b.im;
-    const double scl = 1.0 / (b.im + b.re * rat);
+    const double rat = m.div(b.re, b.im);
+    const double scl = m.div_num_ok(1.0, b.im + b.re * rat);
     r.re = (a.re * rat + a.im) * scl;
     r.im = (a.im * rat - a.re) * scl;
   }
   return r;
 }
+OGG_DI Cx cdivn(Cx a, Cx b) { MathIeee m; return cdivn(m, a, b); }
 OGG_DI Cx cis_np(double t) {  // cos(t) + 1j*sin(t) with numpy's promotions (:451,:495)
   const SinCos q = sincos_parts(t);
   const Cx js = cmul(Cx{0.0, 1.0}, Cx{sin_of(q), 0.0});
@@ -747,13 +776,19 @@ OGG_DI Cx dp_col(double lon, Cx z0) {  // e2ithetaprime (:451-452), a function o
   return cdivn(Cx{e.re - z0.re, e.im - z0.im}, Cx{1.0 - p.re, 0.0 - p.im});
 }
 OGG_DI double dp_row(double lat, double r_joint) { return p_tan((90 + lat) * kPi180) / r_joint; }  // :448
-OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
+template <class M>
+OGG_DI void dp_vertex(M& m, const typename M::Divisor& pi180, double r, Cx ep, const DpConst& K, double& lam_raw,
+                      double& phi) {
   const Cx z = cmul(Cx{r, 0.0}, ep);                                                         // :454
   const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
-  const Cx w = cdivn(Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, 0.0 + q.im});        // :455
-  lam_raw = p_atan2(w.im, w.re) * kC[k180OverPi];                                             // :457
-  const double rw = sqrt(w.re * w.re + w.im * w.im);                                         // :465
-  phi = -90 + p_atan(rw * K.r_joint) / kPi180;                                               // :466
+  const Cx w = cdivn(m, Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, 0.0 + q.im});     // :455
+  lam_raw = p_atan2(m, w.im, w.re) * kC[k180OverPi];                                          // :457
+  const double rw = m.sqrt_(w.re * w.re + w.im * w.im);                                      // :465
+  phi = -90 + m.div_by(p_atan(m, rw * K.r_joint), pi180);                                    // :466
+}
+OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
+  MathIeee m;
+  dp_vertex(m, m.divisor(kPi180), r, ep, K, lam_raw, phi);
 }
 
 __global__ void k_dp_constants(double lat0, double lam_pole, double r_pole, double* __restrict__ out3) {
@@ -873,12 +908,17 @@ __global__ void __launch_bounds__(kScanThreads) k_monotonic(double* __restrict__
 }
 
 // great_arc_distance tail (OGG:527-532) on two projected meshes
-OGG_DI double haversine(double lam0, double phi0, double lam1, double phi1) {
+template <class M>
+OGG_DI double haversine(M& m, double lam0, double phi0, double lam1, double phi1) {
   const double l0 = lam0 * kPi180, p0 = phi0 * kPi180, l1 = lam1 * kPi180, p1 = phi1 * kPi180;
   const double dphi = p1 - p0, dlam = l1 - l0;
   const double s1 = p_sin(0.5 * dphi), s2 = p_sin(0.5 * dlam);
   const double d = s1 * s1 + ((s2 * s2) * p_cos(p0)) * p_cos(p1);  // :531
-  return 2.0 * p_asin(sqrt(d));                                    // :532
+  return 2.0 * p_asin(m, m.sqrt_(d));                              // :532
+}
+OGG_DI double haversine(double lam0, double phi0, double lam1, double phi1) {
+  MathIeee m;
+  return haversine(m, lam0, phi0, lam1, phi1);
 }
 __global__ void __launch_bounds__(256) k_haversine(const double* __restrict__ lam0, const double* __restrict__ phi0,
                                                    const double* __restrict__ lam1, const double* __restrict__ phi1,
@@ -905,8 +945,19 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
 // out-of-line copy for k_dp_hsamples: with the haversine inlined four times next to four inlined projections the
 // kernel's loop body overflowed the instruction cache (stalled_no_instruction 2.1 per issue); one shared copy is 4.5 %
 // faster.  Same instructions, same results.
-__device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
+__device__ __noinline__ double haversine_ieee(double lam0, double phi0, double lam1, double phi1) {
   return haversine(lam0, phi0, lam1, phi1);
+}
+__device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
+  MathFast m;
+  const double v = haversine(m, lam0, phi0, lam1, phi1);
+  return m.ok() ? v : haversine_ieee(lam0, phi0, lam1, phi1);   // e.g. coincident points: sqrt(0), asin(0)
+}
+struct LamPhi { double l, p; };
+__device__ __noinline__ LamPhi dp_vertex_ieee(double r, double epre, double epim, double rj, double z0re, double z0im) {
+  LamPhi o;
+  dp_vertex(r, Cx{epre, epim}, DpConst{rj, Cx{z0re, z0im}}, o.l, o.p);
+  return o;
 }
 // --- fused numerical_hi + numerical_hj on a lattice of unique samples (OGG:583-584) ------------------------------
 // For finite-difference order 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column),
@@ -948,6 +999,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
   __shared__ unsigned shw[2 * kWarps];
   __shared__ unsigned s_state;
   const DpConst K = dp_load(cst);
+  MathFast mf;
+  const MathFast::Divisor pi180 = mf.divisor(kPi180);
   const i64 ntile = (ncol + TW - 1) / TW;
   const i64 nitem = nrow * ntile;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -965,7 +1018,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         const double rv = rr[kind < 2 ? 0 : 2 * lvl + kind - 1];        // r at j (kinds 0,1) or j +- (lvl+1) eps
         const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];            // e' at i +- (lvl+1) eps (kinds 0,1) or i
         double l, p;
-        dp_vertex(rv, ep, K, l, p);
+        mf.reset();
+        dp_vertex(mf, pi180, rv, ep, K, l, p);
+        if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, an axis crossing)
+          const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
+          l = o.l; p = o.p;
+        }
         lamS[m][threadIdx.x] = l;
         phiS[m][threadIdx.x] = p;
       }
@@ -1044,6 +1102,94 @@ __global__ void k_dp_x0(const double* __restrict__ iv, double i0, double eps, i6
   if (kind == 0) idx = first + s;
   if (kind == 1) idx = first - s;
   x0v[m] = lon0 + (idx * 360.0) / (double)ni;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// self-test of the MathFast policy (ogg_trig.cuh) against the compiler's IEEE division / square root
+// ------------------------------------------------------------------------------------------------
+OGG_DI unsigned long long splitmix64(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+// operand generators.  mode 0: random significands, exponents spread over MathFast's whole guarded range;
+// 1: raw random bit patterns (zeros, subnormals, infinities, NaNs, extremes: the guards must reject what the sequence
+// cannot do); 2: significands within a few ulps of 1, 2 and of each other (hard rounding cases: quotients next to a
+// rounding boundary); 3: small-integer significands (exact and half-way quotients).
+OGG_DI double gen_operand(unsigned long long h, int mode) {
+  const unsigned long long mant = h & 0xfffffffffffffull, sign = (h >> 63) << 63;
+  if (mode == 1) {
+    const unsigned sel = (unsigned)(h >> 52) & 7u;
+    if (sel == 0) return __longlong_as_double((long long)(sign | (h & 0xffull)));                // zero / tiny subnormals
+    if (sel == 1) return __longlong_as_double((long long)(sign | 0x7ff0000000000000ull | ((h >> 8) & 1 ? mant : 0)));
+    return __longlong_as_double((long long)h);
+  }
+  const int span = 0x5c0 - 0x240;
+  const unsigned long long e = 0x240 + ((h >> 52) & 0x7ff) % span;
+  if (mode == 2) {
+    const unsigned long long near = (h >> 8) & 1 ? (mant & 0x3f) : (0xfffffffffffffull - (mant & 0x3f));
+    return __longlong_as_double((long long)(sign | (e << 52) | near));
+  }
+  if (mode == 3) return scale2((double)(1 + (mant & 0xfff)), (int)(e % 200) - 100) * (sign ? -1.0 : 1.0);
+  return __longlong_as_double((long long)(sign | (e << 52) | mant));
+}
+// counts[0]: operand sets accepted by the guards; counts[1]: accepted sets whose MathFast result differs in any bit
+// from the IEEE result; counts[2]: sets in MathFast's documented range that a guard rejected (must be 0 for modes != 1)
+__global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long long seed, int mode,
+                                                          unsigned long long* __restrict__ counts) {
+  unsigned long long acc = 0, bad = 0, rej = 0;
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    const unsigned long long h0 = splitmix64(seed + 2ull * (unsigned long long)e), h1 = splitmix64(h0 ^ 0x5851f42d4c957f2dull);
+    const double a = gen_operand(h0, mode), b = gen_operand(h1, mode);
+    MathFast m;
+    const double q = m.div(a, b);
+    if (m.ok()) { ++acc; if (__double_as_longlong(q) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
+    m.reset();
+    const double q1 = m.div_num_ok(1.0, b);
+    if (m.ok()) { ++acc; if (__double_as_longlong(q1) != __double_as_longlong(1.0 / b)) ++bad; } else if (mode != 1) ++rej;
+    m.reset();
+    const MathFast::Divisor d = m.divisor(b);
+    const double q2 = m.div_by(a, d);
+    if (m.ok()) { ++acc; if (__double_as_longlong(q2) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
+    m.reset();
+    const double x = MathFast::abs_(a);
+    const double r = m.sqrt_(x);
+    if (m.ok()) { ++acc; if (__double_as_longlong(r) != __double_as_longlong(sqrt(x))) ++bad; } else if (mode != 1) ++rej;
+    m.reset();
+    const double z = m.div_ok(0.0, MathFast::abs_(b));   // +0 numerators (atan_pos, asin_r) over a positive denominator
+    m.require_moderate(b);
+    if (m.ok()) { ++acc; if (__double_as_longlong(z) != __double_as_longlong(0.0 / MathFast::abs_(b))) ++bad; }
+  }
+  if (acc) atomicAdd(counts, acc);
+  if (bad) atomicAdd(counts + 1, bad);
+  if (rej) atomicAdd(counts + 2, rej);
+}
+// mode 4: the portable functions that divide (tan, arctan, arctan2, arcsin, arccos) under MathFast against the same
+// functions under MathIeee, on arguments spread over [-8, 8] (tan, arctan*), [-1, 1] (arcsin, arccos) and tiny values
+__global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long seed, unsigned long long* __restrict__ counts) {
+  unsigned long long acc = 0, bad = 0;
+  auto same = [](double u, double v) { return __double_as_longlong(u) == __double_as_longlong(v); };
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    const unsigned long long h0 = splitmix64(seed + 2ull * (unsigned long long)e), h1 = splitmix64(h0 ^ 0x5851f42d4c957f2dull);
+    const double u0 = (double)(h0 >> 11) * 0x1p-53, u1 = (double)(h1 >> 11) * 0x1p-53;   // [0, 1)
+    const double scale = (h0 & 7) == 0 ? 1e-9 : 1.0;
+    const double x = (16.0 * u0 - 8.0) * scale, y = (16.0 * u1 - 8.0) * scale, c = (2.0 * u0 - 1.0) * scale;
+    MathFast m;
+    double v = p_tan(m, x);
+    if (m.ok()) { ++acc; if (!same(v, p_tan(x))) ++bad; }
+    m.reset(); v = p_atan(m, x);
+    if (m.ok()) { ++acc; if (!same(v, p_atan(x))) ++bad; }
+    m.reset(); v = p_atan2(m, y, x);
+    if (m.ok()) { ++acc; if (!same(v, p_atan2(y, x))) ++bad; }
+    m.reset(); v = p_asin(m, c);
+    if (m.ok()) { ++acc; if (!same(v, p_asin(c))) ++bad; }
+    m.reset(); v = p_acos(m, c);
+    if (m.ok()) { ++acc; if (!same(v, p_acos(c))) ++bad; }
+  }
+  if (acc) atomicAdd(counts, acc);
+  if (bad) atomicAdd(counts + 1, bad);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1526,6 +1672,12 @@ static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow,
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
+#ifndef OGG_DP_MINB   // tuning knobs of the order-4 instantiation (the one main() uses)
+#define OGG_DP_MINB 5
+#endif
+#ifndef OGG_DP_UNR
+#define OGG_DP_UNR 4
+#endif
 template <typename KERN>
 static int dp_hsamples_launch(KERN kern, int threads, int* per_sm, const Cx* ct, const double* rt, i64 nrow, i64 ncol,
                               const double* x0v, const double* cst, double reps, double* hx, double* hy, cudaStream_t st) {
@@ -1557,7 +1709,7 @@ static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, con
 static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
                        double reps, double* hx, double* hy, cudaStream_t st) {
   if (nv == 1) return dp_hsamples_t<1, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-  if (nv == 2) return dp_hsamples_t<2, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
+  if (nv == 2) return dp_hsamples_t<2, 256, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
   return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
 }
 static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
@@ -1671,6 +1823,19 @@ int ogg_checksum_accumulate(const double* a, int64_t n, uint64_t* acc, void* str
   const unsigned g = (unsigned)(want < (i64)num_sms() * 8 ? want : (i64)num_sms() * 8);
   OGG_LAUNCH(KID_REDUCE, (k_checksum), (g, kRedThreads), (st), a, (i64)n, reinterpret_cast<unsigned long long*>(acc));
   OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_selftest_divsqrt(int64_t n, uint64_t seed, int mode, uint64_t* counts3_host) {
+  if (!counts3_host || n < 1 || mode < 0 || mode > 4) return OGG_ERR_ARG;
+  unsigned long long* dev;
+  OGG_CUDA(cudaMalloc(&dev, 24));
+  OGG_CUDA(cudaMemset(dev, 0, 24));
+  if (mode == 4) k_selftest_trig<<<num_sms() * 8, 256>>>(n, (unsigned long long)seed, dev);
+  else k_selftest_divsqrt<<<num_sms() * 8, 256>>>(n, (unsigned long long)seed, mode, dev);
+  cudaError_t e = cudaMemcpy(counts3_host, dev, 24, cudaMemcpyDeviceToHost);
+  cudaFree(dev);
+  OGG_CUDA(e);
   return OGG_OK;
 }
 

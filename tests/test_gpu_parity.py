@@ -39,6 +39,32 @@ def test_trig_device_equals_oracle(dnp, oracle, name):
     assert_bits(getattr(dnp, name)(x), oracle.unary(name, x), name)
 
 
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+def test_fast_division_and_sqrt_are_ieee(G, mode):
+    """The cap kernels replace the compiler's guarded-and-branching IEEE division / square root by the same
+    instruction sequence with operand-range guards and a per-sample redo (MathFast, csrc/ogg_trig.cuh).  Every result
+    the guards accept must be the IEEE result, bit for bit; in-range operands must not be rejected."""
+    import ctypes
+    from ocean_model_grid_generator_b200 import _cabi
+    lib = _cabi.load()
+    total = 0
+    for seed in (1, 2, 3):
+        counts = (ctypes.c_uint64 * 3)()
+        n = 1 << 27 if mode != 4 else 1 << 25
+        assert lib.ogg_selftest_divsqrt(n, seed * 0x9e3779b9, mode, counts) == 0
+        accepted, differing, rejected = counts[0], counts[1], counts[2]
+        assert differing == 0, "mode %d seed %d: %d of %d accepted results differ from IEEE" % (mode, seed, differing, accepted)
+        assert rejected == 0, "mode %d: %d in-range operand sets rejected" % (mode, rejected)
+        total += accepted
+        if mode in (0, 2, 3):
+            assert accepted == 5 * n          # everything generated in range is accepted
+        elif mode == 1:
+            assert 0 < accepted < 5 * n       # raw bit patterns: the guards reject a share and accept a share
+        else:
+            assert accepted > 4 * n           # trig: only exact zeros / out-of-range quotients are redone
+    assert total > 0
+
+
 def test_arctan2_and_mod(dnp, oracle):
     rng = np.random.default_rng(18)
     y, x = rng.uniform(-2, 2, 500000), rng.uniform(-2, 2, 500000)
