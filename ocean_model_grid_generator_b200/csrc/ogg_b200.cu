@@ -658,24 +658,48 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
   const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
   MathFast mf;
   const MathFast::Divisor pi180 = mf.divisor(kPi180), dnx = mf.divisor((double)nx), dny = mf.divisor((double)ny);
-  for (int s = threadIdx.x; s < SR * SC; s += 256) {
-    const int r = s / SC, c = s - r * SC;
-    const i64 gr = gr0 + r, gc = gc0 + c;
+  // one sample: scaled h_i_inv, h_j_inv of unique row r / column c of this tile -> shared memory
+  auto sample = [&](int r, int c, const BpCol& C, bool col_ok) {
+    const i64 gr = gr0 + r;
     double a = 0.0, b = 0.0;
-    if (gr < nreg && gc < nuc) {
+    if (col_ok && gr < nreg) {
+      const BpRow R = rt[gr];
       double l, p;
       mf.reset();
-      bp_sample<false>(mf, pi180, rt[gr], ct[gc], lon_bp, rp, l, p, a, b);
+      bp_sample<false>(mf, pi180, R, C, lon_bp, rp, l, p, a, b);
       a = mf.div_by((a * 2) * kPi, dnx);                                          // :131
       b = mf.div_by((b * (90 - lat0_bp)) * kPi180, dny);                          // :132
       if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, the lon_bp meridian)
-        const HiHj o = bp_qsample_ieee(rt[gr], ct[gc], lon_bp, rp, lat0_bp, (double)nx, (double)ny);
+        const HiHj o = bp_qsample_ieee(R, C, lon_bp, rp, lat0_bp, (double)nx, (double)ny);
         a = o.a; b = o.b;
       }
     }
     const int pos = r * SCP + (c % (N - 1)) * (TC + 1) + c / (N - 1);
     sx[pos] = a;
     sy[pos] = b;
+  };
+  // a thread keeps ONE sample column (its column-table entry stays in registers, a warp covers 32 consecutive
+  // columns of one row, whose row-table entry is a broadcast load) and walks down the rows, G row-interleaved groups
+  // of SC-1 threads; the tile's last column goes to the first SR threads of the last group, which has the fewest rows.
+  constexpr int CM = SC - 1, G = 256 / CM;
+  const int grp = threadIdx.x / CM, cm = threadIdx.x - grp * CM;
+  if (grp < G) {
+    const bool col_ok = gc0 + cm < nuc;
+    BpCol C{0.0, 0.0, 0.0};
+    if (col_ok) C = ct[gc0 + cm];
+    const bool extra = grp == G - 1 && cm < SR;
+    for (int r = grp;; r += G) {        // one call site: the sample code is large
+      int rr = r, cc = cm;
+      bool ok = col_ok;
+      const bool tail = r >= SR;
+      if (tail) {
+        if (!extra) break;
+        rr = cm; cc = CM; ok = gc0 + CM < nuc;
+        if (ok) C = ct[gc0 + CM];
+      }
+      sample(rr, cc, C, ok);
+      if (tail) break;
+    }
   }
   __syncthreads();
   const int lr = threadIdx.x / TC, li = threadIdx.x - lr * TC;
@@ -964,15 +988,17 @@ __device__ __noinline__ LamPhi dp_vertex_ieee(double r, double epre, double epim
 // each needing its own longitude unwrap along the row: their 2-state maps are packed into one word and scanned
 // together.  Column table ct: [ncol][1+2NV] = e' at {i, i+eps, i-eps, i+2eps, i-2eps, ...}; row table rt likewise.
 //
-// Work item = (sample row, tile of THREADS-1 new columns); item k belongs to CTA k mod gridDim.x of a grid that is
-// co-resident by construction (cooperative launch, one CTA per occupancy slot), so the load is balanced for ANY
-// number of sample rows -- a row-slab on one of 8 GPUs has far fewer rows than there are CTA slots.  Thread 0 of a
-// tile re-evaluates the previous tile's last column (the predecessor raw longitudes of thread 1), so a tile needs
-// from its left neighbours only the shift STATE (one bit per mesh) after that column: a decoupled look-back.  Each
-// tile publishes a 64-bit descriptor: first its aggregate 2-state map, then -- once the state at its left edge is
-// known -- the state after its last column; a tile resolves its left-edge state by walking back over aggregates until
-// it meets a published state (tile 0 of a row knows its state: not shifted).  Every CTA works through its items in
-// increasing order and waits only on lower-numbered items, so the lowest unfinished item can always proceed.
+// Work item = (sample row, tile of THREADS-1 new columns), one item per CTA.  A CTA draws its item number from a
+// ticket counter when it starts running, so item k is always taken by a CTA that is already resident -- no
+// co-residency requirement on the grid (a plain launch: the block scheduler interleaves the CTAs of the other
+// sub-grids' kernels as these retire) and an even load for ANY number of sample rows (a row-slab on one of 8 GPUs
+// has far fewer rows than there are CTA slots).  Thread 0 of a tile re-evaluates the previous tile's last column (the
+// predecessor raw longitudes of thread 1), so a tile needs from its left neighbours only the shift STATE (one bit
+// per mesh) after that column: a decoupled look-back.  Each tile publishes a 64-bit descriptor: first its aggregate
+// 2-state map, then -- once the state at its left edge is known -- the state after its last column; a tile resolves
+// its left-edge state by walking back over aggregates until it meets a published state (tile 0 of a row knows its
+// state: not shifted).  A tile waits only on lower-numbered items, which were drawn earlier by running CTAs, so the
+// lowest unfinished item can always proceed.
 constexpr unsigned long long kDescAgg = 1ull << 62, kDescState = 2ull << 62;
 OGG_DI unsigned long long desc_load(const unsigned long long* p) {
   unsigned long long v;
@@ -984,8 +1010,8 @@ OGG_DI void desc_store(unsigned long long* p, unsigned long long v) {
 }
 // The 4*NV projected meshes of a thread's column are parked in shared memory and the per-mesh work runs in partly
 // rolled loops: fewer live registers, and less code than the fully unrolled form (which misses the instruction cache).
-// Items are numbered tile-major (all rows' tile t before any tile t+1), so that a tile's left neighbour was started
-// nrow items -- most of a grid-wide round -- earlier and its descriptor is normally there when looked for.
+// Items are numbered tile-major (all rows' tile t before any tile t+1), so that a tile's left neighbour was drawn
+// nrow tickets earlier and its descriptor is normally there when looked for.
 template <int NV, int THREADS, int MINB, int UNR>
 __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restrict__ ct, const double* __restrict__ rt,
                                                                  i64 nrow, i64 ncol, const double* __restrict__ x0v,
@@ -1004,7 +1030,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
   const i64 ntile = (ncol + TW - 1) / TW;
   const i64 nitem = nrow * ntile;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  for (i64 item = blockIdx.x; item < nitem; item += gridDim.x) {
+  __shared__ i64 s_item;
+  {
+    if (threadIdx.x == 0) s_item = (i64)atomicAdd(desc + nitem, 1ull);   // the ticket counter follows the descriptors
+    __syncthreads();
+    const i64 item = s_item;
     const i64 t = item / nrow, r = item - t * nrow;
     const i64 c = t * TW + (i64)threadIdx.x - 1;
     const bool virt = c < 0;
@@ -1678,6 +1708,9 @@ static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow,
 #ifndef OGG_DP_UNR
 #define OGG_DP_UNR 4
 #endif
+#ifndef OGG_DP_THREADS
+#define OGG_DP_THREADS 256
+#endif
 template <typename KERN>
 static int dp_hsamples_launch(KERN kern, int threads, int* per_sm, const Cx* ct, const double* rt, i64 nrow, i64 ncol,
                               const double* x0v, const double* cst, double reps, double* hx, double* hy, cudaStream_t st) {
@@ -1685,17 +1718,14 @@ static int dp_hsamples_launch(KERN kern, int threads, int* per_sm, const Cx* ct,
   const i64 nitem = nrow * ntile;
   Scratch ws(st);
   unsigned long long* desc;
-  OGG_CUDA(ws.get(&desc, (size_t)nitem));
-  OGG_CUDA(cudaMemsetAsync(desc, 0, (size_t)nitem * 8, st));
-  if (*per_sm == 0) {
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, kern, threads, 0) != cudaSuccess || *per_sm < 1) *per_sm = 1;
-  }
-  const i64 cap = (i64)num_sms() * *per_sm;
-  const unsigned g = (unsigned)(nitem < cap ? nitem : cap);
+  OGG_CUDA(ws.get(&desc, (size_t)nitem + 1));
+  OGG_CUDA(cudaMemsetAsync(desc, 0, (size_t)(nitem + 1) * 8, st));
+  (void)per_sm;
+  if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
   void* args[] = {(void*)&ct, (void*)&rt, (void*)&nrow, (void*)&ncol, (void*)&x0v, (void*)&cst, (void*)&reps,
                   (void*)&hx, (void*)&hy, (void*)&desc};
   launch_begin(KID_DP_HSAMPLES, st);
-  const cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(g), dim3(threads), args, 0, st);
+  const cudaError_t e = cudaLaunchKernel((const void*)kern, dim3((unsigned)nitem), dim3(threads), args, 0, st);
   launch_end(st);
   OGG_CUDA(e);
   return OGG_OK;
@@ -1709,7 +1739,7 @@ static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, con
 static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
                        double reps, double* hx, double* hy, cudaStream_t st) {
   if (nv == 1) return dp_hsamples_t<1, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-  if (nv == 2) return dp_hsamples_t<2, 256, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
+  if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
   return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
 }
 static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {

@@ -202,6 +202,20 @@ def first_column_latitudes(piece):
 from .slabs import slab_bounds  # noqa: E402  (contiguous split of a piece's cell rows; every rank gets a share of every piece)
 
 
+_POOL = {}
+
+
+def _stream_pool():
+    """Side streams shared by every Supergrid of this process and device (creating a stream costs ~0.1 ms): two of
+    normal priority for the caps' quadratures, four of high priority for everything short; eight reusable events."""
+    import torch
+    dev = torch.cuda.current_device()
+    if dev not in _POOL:
+        _POOL[dev] = ([torch.cuda.Stream(priority=0) for _ in range(2)] + [torch.cuda.Stream(priority=-1) for _ in range(4)],
+                      [torch.cuda.Event() for _ in range(8)])
+    return _POOL[dev]
+
+
 class Supergrid(object):
     """The six arrays (device tensors) of one rank's share of the supergrid."""
 
@@ -210,7 +224,6 @@ class Supergrid(object):
         buffers at slab v (a 1/120-degree grid is 279 GB: one GPU streams it through one slab's worth of HBM)."""
         self.plan = plan
         self._iv = None
-        self._streams = self._events = None
         self._lam_dev = {}
         cap = None
         if capacity_world is not None:
@@ -289,27 +302,40 @@ class Supergrid(object):
                 if host is not None:
                     self._copy_piece_out(host, *job)
             return self
-        if host is None:   # caps first: their long kernels should not wait behind the bands
-            jobs.sort(key=lambda j: {"dp": 0, "bipolar": 1}.get(j[0].kind, 2))
-        else:              # bands first: their rows start crossing PCIe while the caps compute
-            jobs.sort(key=lambda j: {"dp": 1, "bipolar": 2}.get(j[0].kind, 0))
+        # Two FP64-bound quadratures (one per cap) and many short kernels: table set-up, the HBM-bound band fills, the
+        # caps' own coordinate meshes and angles.  The quadratures go on two normal-priority streams, everything else on
+        # high-priority streams, so that the short kernels' CTAs are placed as soon as a quadrature CTA retires instead
+        # of queueing behind 10^4 of them.  With `host`, the bands are queued first and their rows (most of the bytes)
+        # start crossing PCIe at once; a cap's rows follow when both of its halves are done.
         main = torch.cuda.current_stream()
-        if self._streams is None:
-            self._streams = [torch.cuda.Stream() for _ in range(4)]
-            self._events = [torch.cuda.Event() for _ in range(5)]
-        fork = self._events[4]
+        streams, events = _stream_pool()
+        fork = events[6]
         fork.record(main)
-        for n, job in enumerate(jobs):
-            side = self._streams[n % 4]
-            if n < 4:
+        caps = [j for j in jobs if j[0].kind != "band"]
+        bands = [j for j in jobs if j[0].kind == "band"]
+        quads = [] if plan.skip_metrics else [(n % 2, job, "quad") for n, job in enumerate(caps)]
+        light_caps = [(2 + n % 2, job, "mesh") for n, job in enumerate(caps)]
+        light_bands = [(4 + n % 2, job, "all") for n, job in enumerate(bands)]
+        work = (light_bands + quads + light_caps) if host is not None else (quads + light_caps + light_bands)
+        used = set()
+        for sidx, job, part in work:
+            side = streams[sidx]
+            if sidx not in used:
                 side.wait_event(fork)
+                used.add(sidx)
             with torch.cuda.stream(side):
-                self._build_piece(*job)
-                if host is not None:
+                self._build_piece(*job, part=part)
+                if host is not None and part == "all":
                     self._copy_piece_out(host, *job)
-        for n in range(min(len(jobs), 4)):
-            self._events[n].record(self._streams[n])
-            main.wait_event(self._events[n])
+                elif host is not None and part == "mesh":
+                    for qidx, qjob, _ in quads:
+                        if qjob is job:
+                            events[7].record(streams[qidx])
+                            side.wait_event(events[7])
+                    self._copy_piece_out(host, *job)
+        for sidx in sorted(used):
+            events[sidx].record(streams[sidx])
+            main.wait_event(events[sidx])
         return self
 
     def _copy_piece_out(self, host, piece, c0, c1, off, closing):
@@ -330,7 +356,8 @@ class Supergrid(object):
                 _dev.ptr_off(self.dy, off * nxp), _dev.ptr_off(self.area, off * (nxp - 1)),
                 _dev.ptr_off(self.angle_dx, off * nxp), st)
 
-    def _build_piece(self, piece, c0, c1, off, closing):
+    def _build_piece(self, piece, c0, c1, off, closing, part="all"):
+        """part: "all", or for a cap "mesh" (x, y, angle_dx) / "quad" (dx, dy, area) -- independent outputs."""
         plan, nxp = self.plan, self.plan.nxp
         px, py, pdx, pdy, parea, pangle, st = self._views(off, c1 - c0 + 1)
         if plan.skip_metrics:
@@ -352,20 +379,22 @@ class Supergrid(object):
             p = piece.p
             j0, j1 = piece.row0 + c0, piece.row0 + c1
             nv = c1 - c0 + (1 if closing else 0)
-            _cabi.call("ogg_bipolar_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lat0_bp"], p["lon_bp"], p["rp"],
-                       px, py, None, None, st)
-            _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                                # OGG:1071
-            if not plan.skip_metrics:
+            if part != "quad":
+                _cabi.call("ogg_bipolar_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lat0_bp"], p["lon_bp"], p["rp"],
+                           px, py, None, None, st)
+                _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                            # OGG:1071
+            if not plan.skip_metrics and part != "mesh":
                 _cabi.call("ogg_bipolar_cap_metrics_quad", 5, plan.Ni, p["Nj"], j0, j1, p["lat0_bp"], p["lon_bp"],
                            p["rp"], Re, 0 if closing else _cabi.OGG_QUAD_NO_TOP_DX_ROW, pdx, pdy, parea, st)   # OGG:1068
         else:  # displaced pole
             p = piece.p
             j0, j1 = piece.row0 + c0, piece.row0 + c1
             nv = c1 - c0 + (1 if closing else 0)
-            _cabi.call("ogg_dp_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"],
-                       px, py, st)                                                                 # OGG:1162
-            _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                                # OGG:1163
-            if not plan.skip_metrics:
+            if part != "quad":
+                _cabi.call("ogg_dp_cap_mesh", plan.Ni, p["Nj"], j0, j0 + nv, p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"],
+                           px, py, st)                                                             # OGG:1162
+                _cabi.call("ogg_angle_x", px, py, nv, nxp, pangle, st)                            # OGG:1163
+            if not plan.skip_metrics and part != "mesh":
                 _cabi.call("ogg_dp_metrics_quad", 4, plan.Ni, p["Nj"], j0, j1, p["lon0"], p["lat0"], p["lon_dp"],
                            p["r_dp"], Re, 0 if closing else _cabi.OGG_QUAD_NO_TOP_DX_ROW, pdx, pdy, parea, st)  # OGG:1170
 
