@@ -34,9 +34,9 @@ OPS_HAVERSINE = 192 + 1 * W_DIV + 1 * W_SQRT
 OPS_DP_SAMPLE = 8 * OPS_DP_VERTEX + 4 * OPS_HAVERSINE + 8 + 24   # order-4 differences, 8 projections (k_dp_hsamples<2>)
 BYTES_BAND_VERTEX = 48
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the default workload's kernels, from the committed
-# `ncu --set full` capture profiles/r01c_ncu_full_summary.csv -- not measured in this run; valid for `-r 4 --r_dp 0.2` only.
+# `ncu --set full` capture profiles/r01d_ncu_full_summary.csv -- not measured in this run; valid for `-r 4 --r_dp 0.2` only.
 # The cap kernels are FP64-bound and move almost nothing (O(Ni+Nj) tables in, samples parked in the 126 MB L2).
-NCU_TRAFFIC_R4 = {"dp_hsamples": 864000 + 4865280, "bipolar_quad_fused": 343296 + 38656, "band_fill": 326656 + 140826624}
+NCU_TRAFFIC_R4 = {"dp_hsamples": 1533440 + 7467008, "bipolar_quad_fused": 352000 + 32512, "band_fill": 325120 + 142061312}
 
 
 def parse():
@@ -351,7 +351,7 @@ def run_ours(args):
         ach = ops * units[dom] / (per_step_ms * 1e-3) / 1e12
         roof = {"kernel": dom, "bound": "fp64", "achieved": ach, "peak": fp64_peak_tf, "unit": "TFLOP/s", "frac": ach / fp64_peak_tf,
                 "traffic": NCU_TRAFFIC_R4.get(dom) if (r == 4 and world == 1 and not args.slabs) else None,
-                "traffic_source": "profiles/r01c_ncu_full_summary.csv (ncu --set full, bytes per launch)", "ops_per_unit": ops, "units_per_step": units[dom], "kernel_ms_per_step": per_step_ms,
+                "traffic_source": "profiles/r01d_ncu_full_summary.csv (ncu --set full, bytes per launch)", "ops_per_unit": ops, "units_per_step": units[dom], "kernel_ms_per_step": per_step_ms,
                 "share_of_step": per_step_ms / (ms / args.steps),
                 "peak_source": "measured in this run: DADD+DMUL issue rate with FMA contraction off (ogg_fp64_issue_rate); "
                                "MEASURED_PEAKS.json has no FP64 entry"}

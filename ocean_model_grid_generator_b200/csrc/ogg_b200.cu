@@ -1322,7 +1322,10 @@ static int run_quad_cells(int order, const double* sx, const double* sy, i64 nuc
                      nuc, ncr, nx, top_row, Re, dxq, dyq, daq);
 }
 
-constexpr int kBpTileRows = 6, kBpTileCols = 32;  // 53 KB of samples per CTA: 4 CTAs/SM (8x32: 3 CTAs/SM, 3.6 % slower)
+#ifndef OGG_BP_TR
+#define OGG_BP_TR 6
+#endif
+constexpr int kBpTileRows = OGG_BP_TR, kBpTileCols = 32;  // 53 KB of samples per CTA: 4 CTAs/SM (8x32: 3 CTAs/SM, 3.6 % slower)
 template <int N>
 static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
                                 double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
@@ -1352,9 +1355,6 @@ static int run_bp_quad_fused(int order, const BpCol* ct, const BpRow* rt, i64 nu
 
 // cap on the per-chunk sample scratch of the quadrature drivers (bytes of dx+dy samples)
 static const i64 kQuadChunkBytes = (i64)1 << 30;
-
-static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow, i64 ni, i64 nj, double lon0,
-                         double lat0, const double* cst, int nv, double eps, Cx* ct, double* rt, cudaStream_t st);
 
 }  // namespace ogg
 
@@ -1672,35 +1672,50 @@ int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1,
 
 namespace ogg {
 // tables for the fused h-sample kernel: ct [ncol][1+2nv], rt [nrow][1+2nv] (centre, +eps, -eps, +2eps, -2eps, ...)
-__global__ void __launch_bounds__(256) k_dp_tables_multi(const double* __restrict__ iv, i64 ncol,
-                                                         const double* __restrict__ jv, i64 nrow, i64 ni, i64 nj,
-                                                         double lon0, double lat0, const double* __restrict__ cst, int nv,
-                                                         double eps, Cx* __restrict__ ct, double* __restrict__ rt) {
-  const DpConst K = dp_load(cst);
-  const int nt = 1 + 2 * nv;
+// Everything k_dp_hsamples needs, in one launch (it used to be six short launches in front of the critical path):
+// the projection constants (:494-495), the unique sample indices (:573-581), the column / row tables of e' and r at
+// the centre and at +-eps, +-2eps.. (:538-559), the x_0 of every shifted mesh (:463, :479) and the cleared look-back
+// descriptors + ticket counter.  Every thread derives the constants itself (a tan and a sincos) instead of waiting
+// for another kernel to publish them; thread 0 stores them for the kernels that follow.
+__global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i64 nx, i64 ny, i64 c0, i64 c1, int do_cols,
+                                                       double lon0, double lat0, double lam_pole, double r_pole, int nv,
+                                                       double eps, double* __restrict__ cst, Cx* __restrict__ ct,
+                                                       double* __restrict__ rt, double* __restrict__ x0v,
+                                                       unsigned long long* __restrict__ desc, i64 ndesc) {
   const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  DpConst K;
+  K.r_joint = p_tan((90 + lat0) * kPi180);                                                 // :494
+  K.z0 = cmul(Cx{r_pole, 0.0}, cis_np(lam_pole * kPi180));                                 // :495
+  if (t == 0) { cst[0] = K.r_joint; cst[1] = K.z0.re; cst[2] = K.z0.im; }
+  const int nt = 1 + 2 * nv;
+  const i64 nuc = (order - 1) * nx + 1, nur = (order - 1) * (c1 - c0) + 1;
+  const bool col = do_cols && t < nuc, row = t < nur;
+  const double ic = col ? sample_index_at(q, order, 0, nx, nx, 0, t) : 0.0;                // :578-581
+  const double jc = row ? sample_index_at(q, order, c0, c1, ny, 0, t) : 0.0;               // :573-576
   for (int k = 0; k < nt; ++k) {
     const int lvl = (k + 1) / 2;  // 0 centre, 1: eps, 2: 2eps, 3: 3eps
     const double s = lvl == 1 ? eps : (lvl == 2 ? 2.0 * eps : 3.0 * eps);
     const bool plus = (k & 1) == 1;
-    if (ct && t < ncol) {
-      const double idx = k == 0 ? iv[t] : (plus ? iv[t] + s : iv[t] - s);            // :538,:541,:544
-      ct[t * nt + k] = dp_col(lon0 + (idx * 360.0) / (double)ni, K.z0);
+    if (col) {
+      const double idx = k == 0 ? ic : (plus ? ic + s : ic - s);                           // :538,:541,:544
+      ct[t * nt + k] = dp_col(lon0 + (idx * 360.0) / (double)nx, K.z0);
     }
-    if (rt && t < nrow) {
-      const double idx = k == 0 ? jv[t] : (plus ? jv[t] + s : jv[t] - s);            // :553,:556,:559
+    if (row) {
+      const double idx = k == 0 ? jc : (plus ? jc + s : jc - s);                           // :553,:556,:559
       const double a = -90.0, b = lat0;
-      rt[t * nt + k] = dp_row(a + (idx * (b - a)) / (double)nj, K.r_joint);
+      rt[t * nt + k] = dp_row(a + (idx * (b - a)) / (double)ny, K.r_joint);
     }
   }
-}
-static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow, i64 ni, i64 nj, double lon0, double lat0,
-                         const double* cst, int nv, double eps, Cx* ct, double* rt, cudaStream_t st) {
-  const i64 m = (ct ? ncol : 0) > (rt ? nrow : 0) ? (ct ? ncol : 0) : (rt ? nrow : 0);
-  if (m == 0) return OGG_OK;
-  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables_multi), (cdiv_u(m, 256), 256), (st), iv, ncol, jv, nrow, ni, nj, lon0, lat0, cst, nv, eps, ct, rt);
-  OGG_LAUNCH_CHECK();
-  return OGG_OK;
+  if (do_cols && t < 4 * nv) {                                                             // x_0 of mesh t (k_dp_x0)
+    const int lvl = (int)t / 4, kind = (int)t % 4;
+    const double s = lvl == 0 ? eps : (lvl == 1 ? 2.0 * eps : 3.0 * eps);
+    const double first = sample_index_at(q, order, 0, nx, nx, 0, 0);
+    double idx = first;
+    if (kind == 0) idx = first + s;
+    if (kind == 1) idx = first - s;
+    x0v[t] = lon0 + (idx * 360.0) / (double)nx;
+  }
+  for (i64 e = t; e < ndesc; e += (i64)gridDim.x * blockDim.x) desc[e] = 0ull;
 }
 #ifndef OGG_DP_MINB   // tuning knobs of the order-4 instantiation (the one main() uses)
 #define OGG_DP_MINB 5
@@ -1711,43 +1726,27 @@ static int dp_tables_for(const double* iv, i64 ncol, const double* jv, i64 nrow,
 #ifndef OGG_DP_THREADS
 #define OGG_DP_THREADS 256
 #endif
-template <typename KERN>
-static int dp_hsamples_launch(KERN kern, int threads, int* per_sm, const Cx* ct, const double* rt, i64 nrow, i64 ncol,
-                              const double* x0v, const double* cst, double reps, double* hx, double* hy, cudaStream_t st) {
-  const i64 ntile = (ncol + threads - 2) / (threads - 1);
-  const i64 nitem = nrow * ntile;
-  Scratch ws(st);
-  unsigned long long* desc;
-  OGG_CUDA(ws.get(&desc, (size_t)nitem + 1));
-  OGG_CUDA(cudaMemsetAsync(desc, 0, (size_t)(nitem + 1) * 8, st));
-  (void)per_sm;
-  if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
-  void* args[] = {(void*)&ct, (void*)&rt, (void*)&nrow, (void*)&ncol, (void*)&x0v, (void*)&cst, (void*)&reps,
-                  (void*)&hx, (void*)&hy, (void*)&desc};
-  launch_begin(KID_DP_HSAMPLES, st);
-  const cudaError_t e = cudaLaunchKernel((const void*)kern, dim3((unsigned)nitem), dim3(threads), args, 0, st);
-  launch_end(st);
-  OGG_CUDA(e);
-  return OGG_OK;
+// nitem descriptors + the ticket counter, all zero before the launch (k_dp_quad_setup clears them)
+static i64 dp_hsamples_items(int nv, i64 nrow, i64 ncol) {
+  const int threads = nv == 3 ? 128 : OGG_DP_THREADS;
+  return nrow * ((ncol + threads - 2) / (threads - 1));
 }
 template <int NV, int THREADS, int MINB, int UNR>
 static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
-                         double reps, double* hx, double* hy, cudaStream_t st) {
-  static int per_sm = 0;   // per instantiation
-  return dp_hsamples_launch(k_dp_hsamples<NV, THREADS, MINB, UNR>, THREADS, &per_sm, ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-}
-static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
-                       double reps, double* hx, double* hy, cudaStream_t st) {
-  if (nv == 1) return dp_hsamples_t<1, 256, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-  if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-  return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, st);
-}
-static int dp_x0(int nv, const double* iv, double eps, i64 ni, double lon0, double* x0v, cudaStream_t st) {
-  if (nv == 1) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
-  else if (nv == 2) OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<2>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
-  else OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<3>), (1, 32), (st), iv, 0.0, eps, ni, lon0, x0v);
+                         double reps, double* hx, double* hy, unsigned long long* desc, cudaStream_t st) {
+  const i64 nitem = nrow * ((ncol + THREADS - 2) / (THREADS - 1));
+  if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
+  launch_begin(KID_DP_HSAMPLES, st);
+  k_dp_hsamples<NV, THREADS, MINB, UNR><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc);
+  launch_end(st);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
+}
+static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
+                       double reps, double* hx, double* hy, unsigned long long* desc, cudaStream_t st) {
+  if (nv == 1) return dp_hsamples_t<1, OGG_DP_THREADS, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
+  if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
+  return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
 }
 }  // namespace ogg
 
@@ -1802,28 +1801,25 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
   const i64 max_cr = rows_per_chunk < (j1 - j0) ? rows_per_chunk : (j1 - j0);
   const i64 max_nur = (order - 1) * max_cr + 2;
   Scratch ws(st);
-  double *cst, *iv, *jv, *rt, *x0v, *sx, *sy;
+  double *cst, *rt, *x0v, *sx, *sy;
   Cx* ct;
-  OGG_CUDA(ws.get(&cst, 3)); OGG_CUDA(ws.get(&iv, nuc + 1)); OGG_CUDA(ws.get(&jv, max_nur));
+  unsigned long long* desc;
+  const i64 max_items = dp_hsamples_items(nv, max_nur, nuc);
+  OGG_CUDA(ws.get(&cst, 3));
   OGG_CUDA(ws.get(&ct, nuc * nt)); OGG_CUDA(ws.get(&rt, max_nur * nt)); OGG_CUDA(ws.get(&x0v, 12));
   OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
-  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lon_dp, r_dp, cst);
-  OGG_LAUNCH_CHECK();
-  OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nuc + 1, 256), 256), (st), q, order, 0, nx, nx, 0, iv);       // :578-581
-  OGG_LAUNCH_CHECK();
-  int rc = dp_tables_for(iv, nuc, nullptr, 0, nx, ny, lon0, lat0, cst, nv, eps, ct, nullptr, st);
-  if (rc) return rc;
-  rc = dp_x0(nv, iv, eps, nx, lon0, x0v, st);
-  if (rc) return rc;
+  OGG_CUDA(ws.get(&desc, (size_t)max_items + 1));
+  int rc;
   for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
     const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
     const bool top = c1 == ny && !(flags & OGG_QUAD_NO_TOP_DX_ROW);
     const i64 nur = (order - 1) * (c1 - c0) + 1;                                           // closing row = row ny when top
-    OGG_LAUNCH(KID_SAMPLE_INDEX, (k_sample_index), (cdiv_u(nur + 1, 256), 256), (st), q, order, c0, c1, ny, 0, jv);    // :573-576
+    const i64 ndesc = dp_hsamples_items(nv, nur, nuc) + 1;
+    const i64 nthr = c0 == j0 ? (nuc > nur ? nuc : nur) : nur;
+    OGG_LAUNCH(KID_DP_SETUP, (k_dp_quad_setup), (cdiv_u(nthr, 256), 256), (st), q, order, nx, ny, c0, c1, c0 == j0 ? 1 : 0,
+               lon0, lat0, lon_dp, r_dp, nv, eps, cst, ct, rt, x0v, desc, ndesc);
     OGG_LAUNCH_CHECK();
-    rc = dp_tables_for(nullptr, 0, jv, nur, nx, ny, lon0, lat0, cst, nv, eps, nullptr, rt, st);
-    if (rc) return rc;
-    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, st);
+    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, desc, st);
     if (rc) return rc;
     rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
                         dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
