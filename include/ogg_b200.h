@@ -49,6 +49,11 @@ int ogg_sinh(const double* in, double* out, int64_t n, void* stream);
 int ogg_cosh(const double* in, double* out, int64_t n, void* stream);
 int ogg_mod360(const double* in, double* out, int64_t n, void* stream); /* numpy.mod(x, 360.0), OGG:684 */
 int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* stream);
+/* y_mercator (OGG:292-295): out = R * log((1 + sin(phi)) / cos(phi)), phi in radians, R = Ni / (2 pi) from the caller.
+ * phi_mercator (OGG:298-301): out = arctan(sinh(y / R)) * (180 / pi); y == NULL means y[t] = y_first + t, the
+ * numpy.arange(y_star[0], y_star[1] + 1) of OGG:336.  One launch each instead of one per elementary function. */
+int ogg_y_mercator(const double* phi, int64_t n, double R, double* out, void* stream);
+int ogg_phi_mercator(const double* y, int64_t n, double y_first, double R, double* out, void* stream);
 
 /* ---- spherical bands (Mercator / Southern Ocean / regular cap) ------------------------------------------ */
 /* Fused tile + MIDAS metrics + angle for a band whose mesh is the outer product of lam[nxp] and phi[nyp]:

@@ -26,6 +26,7 @@ SIGNATURES = {
     "ogg_exp": [_dp, _dp, _i64, _vp], "ogg_log": [_dp, _dp, _i64, _vp], "ogg_sinh": [_dp, _dp, _i64, _vp],
     "ogg_cosh": [_dp, _dp, _i64, _vp], "ogg_mod360": [_dp, _dp, _i64, _vp],
     "ogg_arctan2": [_dp, _dp, _dp, _i64, _vp],
+    "ogg_y_mercator": [_dp, _i64, _d, _dp, _vp], "ogg_phi_mercator": [_dp, _i64, _d, _d, _dp, _vp],
     "ogg_band_fill_metrics": [_dp, _dp, _i64, _i64, _d, _int, _dp, _dp, _dp, _dp, _dp, _dp, _vp],
     "ogg_metrics_midas": [_dp, _dp, _i64, _i64, _d, _int, _dp, _dp, _dp, _dp, _dp, _vp],
     "ogg_angle_x": [_dp, _dp, _i64, _i64, _dp, _vp],

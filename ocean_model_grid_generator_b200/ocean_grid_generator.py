@@ -184,16 +184,35 @@ def lagrange_interp_6pt(x, y, q):
     return _lagrange(list(x[:6]), list(y[:6]), q)
 
 
+def _mercator_law(name, v, R, y_first=None, n=None):
+    """One fused launch of a 1-D Mercator law (ogg_y_mercator / ogg_phi_mercator); numpy in -> numpy out."""
+    if v is None:
+        out = _dev.empty(int(n))
+        _cabi.call(name, None, int(n), float(y_first), float(R), _dev.ptr(out), _dev.stream())
+        return _dev.to_host(out)
+    scalar = numpy.ndim(v) == 0 and not _dev.is_dev(v)
+    t = _dev.to_dev(numpy.atleast_1d(v) if scalar else v)
+    out = _dev.empty(*t.shape)
+    if name == "ogg_y_mercator":
+        _cabi.call(name, _dev.ptr(t), t.numel(), float(R), _dev.ptr(out), _dev.stream())
+    else:
+        _cabi.call(name, _dev.ptr(t), t.numel(), 0.0, float(R), _dev.ptr(out), _dev.stream())
+    if _dev.is_dev(v):
+        return out
+    h = _dev.to_host(out)
+    return numpy.float64(h[0]) if scalar else h
+
+
 def y_mercator(Ni, phi):
-    """Equation (1) (OGG:292-295)."""
+    """Equation (1) (OGG:292-295): R * log((1 + sin(phi)) / cos(phi))."""
     R = Ni / (2 * np.pi)
-    return R * (np.log((1.0 + np.sin(phi)) / np.cos(phi)))
+    return _mercator_law("ogg_y_mercator", phi, R)
 
 
 def phi_mercator(Ni, y):
-    """Equation (2) (OGG:298-301), degrees."""
+    """Equation (2) (OGG:298-301), degrees: arctan(sinh(y / R)) * (180 / pi)."""
     R = Ni / (2 * np.pi)
-    return np.arctan(np.sinh(y / R)) * (180 / np.pi)
+    return _mercator_law("ogg_phi_mercator", y, R)
 
 
 def d_phi_mercator_dy(Ni, y):
@@ -230,7 +249,7 @@ def mercator_latitudes(Ni, phi_s, phi_n, refineR, shift_equator_to_u_point=True,
             print("  *Fixing this by shifting the y_star[1] ")
             y_star[1] = y_star[1] - 1
     print("   Generating Mercator grid with phi range: phi_s,phi_n=", phi_mercator(Ni, y_star))
-    phi_M = phi_mercator(Ni, numpy.arange(y_star[0], y_star[1] + 1))
+    phi_M = _mercator_law("ogg_phi_mercator", None, Ni / (2 * np.pi), y_first=y_star[0], n=y_star[1] - y_star[0] + 1)  # OGG:336
     equator_index = numpy.searchsorted(phi_M, 0.0)
     if equator_index == 0:
         raise Exception("   Ooops: Equator is not in the grid")

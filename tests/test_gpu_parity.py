@@ -231,6 +231,24 @@ def test_mercator_golden(G, golden):
         assert_bits(x[0], -300. + np.arange(Ni + 1) * 360 / float(Ni), "mercator lam")
 
 
+def test_mercator_laws_fused_equal_chain(G, dnp, oracle):
+    """y_mercator / phi_mercator (OGG:292-301) as one launch each: same bits as the reference's chain of element-wise
+    calls (the device functions one by one, numpy's IEEE operations in between) and as the CPU oracle."""
+    rng = np.random.default_rng(41)
+    for Ni in (180, 2880, 21600):
+        R = Ni / (2 * np.pi)
+        phi = np.concatenate([rng.uniform(-1.4, 1.4, 5000), [0.0, -66.85954725 * np.pi / 180, 64.05895973 * np.pi / 180]])
+        chain = R * dnp.log((1.0 + dnp.sin(phi)) / dnp.cos(phi))
+        assert_bits(G.y_mercator(Ni, phi), chain, "y_mercator chain Ni=%d" % Ni)
+        assert_bits(G.y_mercator(Ni, phi), oracle.y_mercator(Ni, phi), "y_mercator oracle Ni=%d" % Ni)
+        y = np.arange(-int(1.3 * R) - 1, int(1.25 * R) + 1).astype(np.float64)
+        chain = dnp.arctan(dnp.sinh(y / R)) * (180 / np.pi)
+        assert_bits(G.phi_mercator(Ni, y), chain, "phi_mercator chain Ni=%d" % Ni)
+        assert_bits(G.phi_mercator(Ni, y), oracle.phi_mercator(Ni, y), "phi_mercator oracle Ni=%d" % Ni)
+        assert_bits(G._mercator_law("ogg_phi_mercator", None, R, y_first=y[0], n=y.size), chain, "phi_mercator arange")
+        assert float(G.phi_mercator(Ni, 3.0)) == float(chain[np.where(y == 3.0)[0][0]])        # scalar path
+
+
 @pytest.mark.parametrize("shape", [(33, 130), (64, 129), (65, 31), (2, 2), (200, 1441)])
 def test_midas_general_vs_oracle(G, oracle, shape):
     rng = np.random.default_rng(31)

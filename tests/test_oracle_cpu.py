@@ -208,3 +208,37 @@ def test_sqrt_of_square_identity():
     edge = np.array([1.0, 1.5, np.nextafter(2.0, 0), np.nextafter(1.0, 2), 2.0 ** -499, 2.0 ** 499, np.sqrt(2.0), 3.0, 1e-3, 7e-17])
     for v in (t, edge, np.nextafter(edge, 0), np.nextafter(edge, np.inf)):
         assert (np.sqrt(0.0 + v * v) == np.abs(v)).all()
+
+
+def test_netcdf3_writer_layout_cpu(tmp_path):
+    """write_nc's container (OGG:795-821): CDF-2 magic, the reference's dimension / variable creation order, units,
+    global attributes, big-endian doubles -- read back with scipy's independent classic-format reader (host-only logic)."""
+    import numpy as np
+    from scipy.io import netcdf_file
+    from ocean_model_grid_generator_b200 import netcdf3
+    rng = np.random.default_rng(5)
+    ny, nx = 7, 10
+    a = {"x": rng.normal(size=(ny + 1, nx + 1)), "y": rng.normal(size=(ny + 1, nx + 1)), "dx": rng.normal(size=(ny + 1, nx)),
+         "dy": rng.normal(size=(ny, nx + 1)), "area": rng.normal(size=(ny, nx)), "angle_dx": rng.normal(size=(ny + 1, nx + 1))}
+    out = tmp_path / "g.nc"
+    netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"],
+                            global_attrs=[("history", "h"), ("description", "some text"), ("source", "s")])
+    raw = out.read_bytes()
+    assert raw[:4] == b"CDF\x02" and raw[4:8] == b"\x00\x00\x00\x00"          # 64-bit offsets, no record dimension
+    header_doubles = 8 * sum(v.size for v in a.values())
+    assert len(raw) > header_doubles and (len(raw) - header_doubles - 256) % 4 == 0
+    f = netcdf_file(str(out), "r", mmap=False)
+    assert list(f.dimensions.items()) == [("nyp", ny + 1), ("nxp", nx + 1), ("ny", ny), ("nx", nx), ("string", 255)]
+    assert list(f.variables) == ["tile", "y", "x", "dy", "dx", "area", "angle_dx"]
+    assert f.variables["tile"][:5].tobytes() == b"tile1" and f.variables["tile"][5:].tobytes() == b"\x00" * 250
+    units = {"y": b"degrees", "x": b"degrees", "dy": b"meters", "dx": b"meters", "area": b"m2", "angle_dx": b"degrees"}
+    for k, u in units.items():
+        assert f.variables[k].units == u
+        assert (np.array(f.variables[k][:], dtype=np.float64).view(np.int64) == a[k].view(np.int64)).all(), k
+    assert f.history == b"h" and f.description == b"some text" and f.source == b"s"
+    f.close()
+    # data blocks follow the header in definition order, contiguous and big-endian
+    tail = raw[len(raw) - 8 * a["angle_dx"].size:]
+    assert tail == a["angle_dx"].astype(">f8").tobytes()
+    with __import__("pytest").raises(ValueError):
+        netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], format="NETCDF4")
