@@ -1394,6 +1394,39 @@ int ogg_timing_enable(int on) {
   g_timing = on < 0 ? 0 : (on > 2 ? 1 : on);
   return OGG_OK;
 }
+// Two kernel classes that run concurrently on different streams (the two cap quadratures): the k-th launch of `id_a`
+// is paired with the k-th launch of `id_b` and the pair's busy span = latest end - earliest start is summed.  A class
+// with fewer launches (a rank whose slab has no rows of one cap) contributes its own duration only.
+int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* pairs) {
+  if (id_a < 0 || id_a >= KID_COUNT || id_b < 0 || id_b >= KID_COUNT || !ms_total || !pairs) return OGG_ERR_ARG;
+  std::vector<const TimedLaunch*> a, b;
+  for (auto& t : g_timed) {
+    if (t.id == id_a) a.push_back(&t);
+    else if (t.id == id_b) b.push_back(&t);
+  }
+  double tot = 0.0;
+  const size_t n = a.size() > b.size() ? a.size() : b.size();
+  for (size_t k = 0; k < n; ++k) {
+    const TimedLaunch* x = k < a.size() ? a[k] : nullptr;
+    const TimedLaunch* y = k < b.size() ? b[k] : nullptr;
+    if (!x) { x = y; y = nullptr; }
+    OGG_CUDA(cudaEventSynchronize(x->e1));
+    float ea = 0.f, sb = 0.f, eb = 0.f;
+    OGG_CUDA(cudaEventElapsedTime(&ea, x->e0, x->e1));
+    double lo = 0.0, hi = ea;
+    if (y) {
+      OGG_CUDA(cudaEventSynchronize(y->e1));
+      OGG_CUDA(cudaEventElapsedTime(&sb, x->e0, y->e0));   // negative if y started first
+      OGG_CUDA(cudaEventElapsedTime(&eb, x->e0, y->e1));
+      if (sb < lo) lo = sb;
+      if (eb > hi) hi = eb;
+    }
+    tot += hi - lo;
+  }
+  *ms_total = tot;
+  *pairs = (long long)n;
+  return OGG_OK;
+}
 int ogg_timing_reset(void) {
   for (auto& t : g_timed) { g_event_pool.push_back(t.e0); g_event_pool.push_back(t.e1); }
   g_timed.clear();
