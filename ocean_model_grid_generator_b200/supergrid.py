@@ -206,13 +206,16 @@ _POOL = {}
 
 
 def _stream_pool():
-    """Side streams shared by every Supergrid of this process and device (creating a stream costs ~0.1 ms): two of
-    normal priority for the caps' quadratures, four of high priority for everything short; eight reusable events."""
+    """Side streams shared by every Supergrid of this process and device (creating a stream costs ~0.1 ms): two for the
+    caps' quadratures, four of higher priority for everything short; eight reusable events."""
     import torch
     dev = torch.cuda.current_device()
     if dev not in _POOL:
-        _POOL[dev] = ([torch.cuda.Stream(priority=0) for _ in range(2)] + [torch.cuda.Stream(priority=-1) for _ in range(4)],
-                      [torch.cuda.Event() for _ in range(8)])
+        # measured at r=4 (tools/stepbench.py): all equal 0.977 ms, short kernels above the quadratures 0.972, and the
+        # second cap's quadrature (the cheaper bipolar one, which then finishes first and frees the SMs for the
+        # displaced-pole tail) above the first 0.966
+        _POOL[dev] = ([torch.cuda.Stream(priority=0), torch.cuda.Stream(priority=-1)] +
+                      [torch.cuda.Stream(priority=-2) for _ in range(4)], [torch.cuda.Event() for _ in range(8)])
     return _POOL[dev]
 
 
