@@ -129,6 +129,13 @@ class ClockSampler(object):
 # ------------------------------------------------------------------------------------------------------
 # CPU arm (oracle): the reference's algorithm restated in C, all host threads
 # ------------------------------------------------------------------------------------------------------
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 for every rank; the CPU arm runs on rank 0 alone and is to use every host
+    thread, so the limit is lifted before the OpenMP runtime of the oracle library starts."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(n)
+
+
 def cpu_pass(r, r_dp):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import supergrid_cpu
@@ -156,6 +163,7 @@ def run_reference(args):
     r, wl = workload(args)
     rr = r if r <= 4 else 4
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    use_all_host_threads()
     import ogg_oracle
     cores = ogg_oracle.num_threads()
     for _ in range(min(args.warmup, 1)):
