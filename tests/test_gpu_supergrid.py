@@ -237,3 +237,68 @@ def test_eighth_degree_equals_cpu_oracle(SG, oracle, r):
         assert_bits(got[k], ref[k], "r=%d %s" % (r, k))
     tot = ref["area"].sum()
     assert abs(got["area"].sum() - tot) <= 1e-12 * tot
+
+
+@pytest.mark.parametrize("rank,world", [(0, 1), (1, 3), (2, 3)])
+def test_build_into_pinned_host_buffers(SG, rank, world):
+    """The end-to-end call of bench.py: build(host=pinned) copies each sub-grid out on its own stream while the caps
+    compute.  Host buffers == a plain build read back afterwards; concurrent == single-stream build, bit for bit."""
+    import torch
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 1 --r_dp 0.2")))
+    ref = SG.Supergrid(plan, rank, world).build(concurrent=False)
+    torch.cuda.synchronize()
+    want = ref.to_host()
+    sg = SG.Supergrid(plan, rank, world)
+    pinned = sg.pinned_like()
+    for v in pinned.values():
+        v.fill_(-7.0)
+    for _ in range(2):                                   # the second call reuses streams, events and buffers
+        sg.build(host=pinned)
+        torch.cuda.synchronize()
+        got_dev = sg.to_host()
+        for k in NAMES:
+            assert_bits(pinned[k].numpy(), want[k], "pinned %s rank %d/%d" % (k, rank, world))
+            assert_bits(got_dev[k], want[k], "concurrent %s rank %d/%d" % (k, rank, world))
+
+
+def test_skip_metrics_leaves_minus_one(SG):
+    """--skip_metrics (OGG:1009-1011, 1069-1071, ...): coordinates and angles as usual, dx / dy / area stay -1."""
+    a = _args("-r 1 --r_dp 0.2")
+    full = SG.build_supergrid(SG.plan_supergrid(**_plan_args(a))).to_host()
+    a["skip_metrics"] = True
+    got = SG.build_supergrid(SG.plan_supergrid(**_plan_args(a))).to_host()
+    for k in ("x", "y", "angle_dx"):
+        assert_bits(got[k], full[k], "skip_metrics " + k)
+    for k in ("dx", "dy", "area"):
+        assert got[k].shape == full[k].shape and (got[k] == -1.0).all(), k
+
+
+def test_timing_brackets_and_pair_span(SG):
+    """ogg_timing_*: per-class totals and the busy span of the two co-running cap quadratures (bench.py's roofline)."""
+    import ctypes
+    import torch
+    from ocean_model_grid_generator_b200 import _cabi
+    lib = _cabi.load()
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 2 --r_dp 0.2")))
+    sg = SG.Supergrid(plan)
+    sg.build(); torch.cuda.synchronize()
+    kid = {lib.ogg_timing_name(k).decode(): k for k in range(lib.ogg_timing_kernels())}
+    lib.ogg_timing_reset(); lib.ogg_timing_enable(2)
+    n0 = lib.ogg_launch_count()
+    for _ in range(3):
+        sg.build()
+    torch.cuda.synchronize()
+    lib.ogg_timing_enable(0)
+    assert lib.ogg_launch_count() - n0 >= 3 * 10
+
+    def total(name):
+        t, n = ctypes.c_double(), ctypes.c_longlong()
+        assert lib.ogg_timing_get(kid[name], ctypes.byref(t), ctypes.byref(n)) == 0
+        return t.value, n.value
+    (tdp, ndp), (tbp, nbp) = total("dp_hsamples"), total("bipolar_quad_fused")
+    span, pairs = ctypes.c_double(), ctypes.c_longlong()
+    assert lib.ogg_timing_pair_span(kid["dp_hsamples"], kid["bipolar_quad_fused"], ctypes.byref(span), ctypes.byref(pairs)) == 0
+    assert ndp == nbp == pairs.value == 3 and tdp > 0 and tbp > 0
+    assert max(tdp, tbp) <= span.value * 1.001 and span.value <= (tdp + tbp) * 1.5 + 1.0
+    lib.ogg_timing_reset()
+    assert total("dp_hsamples") == (0.0, 0)
