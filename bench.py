@@ -42,7 +42,7 @@ NCU_TRAFFIC_R4 = {"dp_hsamples": 774144 + 6492672, "bipolar_quad_fused": 352256 
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--steps", type=int, default=100)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--resolution", type=float, default=0.0, help="override inverse resolution r (default: per --gpus)")
