@@ -245,7 +245,7 @@ def run_ours(args):
     # ---- timed region: K steps, CUDA events on the launching stream, per-kernel events inside --------------
     sampler = ClockSampler(local)
     lib.ogg_timing_reset()
-    lib.ogg_timing_enable(2)     # event brackets around the three heavy kernel classes only (6 launches of ~26 per step)
+    lib.ogg_timing_enable(2)     # event brackets around the three heavy kernel classes only (4 launches of 21 per step)
     l0 = lib.ogg_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()

@@ -149,9 +149,9 @@ int ogg_timing_kernels(void);          /* number of kernel classes */
 const char* ogg_timing_name(int id);   /* class name, e.g. "dp_hsamples" */
 /* total milliseconds and launch count of class `id` since the last reset (synchronises on the recorded events) */
 int ogg_timing_get(int id, double* ms_total, long long* launches);
-/* two classes that run concurrently on different streams: sum over k of (latest end - earliest start) of the k-th
-   launches of id_a and id_b -- the time during which at least one of the pair was in flight */
-int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* pairs);
+/* two classes that run concurrently on different streams: length of the union of the [start, end] intervals of all
+   their bracketed launches -- the time during which at least one of them was in flight; *launches = intervals used */
+int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* launches);
 
 /* ---- measurement aid: FP64 add/mul issue rate (no FMA), the cap kernels' roofline denominator ------------------------ */
 /* runs iters dependent DADD/DMUL pairs x 8 independent chains per thread on every SM; returns via *gops_host the

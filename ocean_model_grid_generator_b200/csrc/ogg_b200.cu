@@ -5,10 +5,12 @@
 // "OGG:n" = /root/reference/ocean_grid_generator.py line n.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <utility>
 #include <vector>
 
 #include "../../include/ogg_b200.h"
@@ -1394,37 +1396,34 @@ int ogg_timing_enable(int on) {
   g_timing = on < 0 ? 0 : (on > 2 ? 1 : on);
   return OGG_OK;
 }
-// Two kernel classes that run concurrently on different streams (the two cap quadratures): the k-th launch of `id_a`
-// is paired with the k-th launch of `id_b` and the pair's busy span = latest end - earliest start is summed.  A class
-// with fewer launches (a rank whose slab has no rows of one cap) contributes its own duration only.
-int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* pairs) {
-  if (id_a < 0 || id_a >= KID_COUNT || id_b < 0 || id_b >= KID_COUNT || !ms_total || !pairs) return OGG_ERR_ARG;
-  std::vector<const TimedLaunch*> a, b;
+// Two kernel classes that run concurrently on different streams (the two cap quadratures): total time during which at
+// least one bracketed launch of either class was in flight = length of the union of their [start, end] intervals
+// (event times taken relative to the first bracketed launch).  Any number of launches per class (a cap's quadrature is
+// chunked on large grids, a rank may hold several slabs per step).
+int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* launches) {
+  if (id_a < 0 || id_a >= KID_COUNT || id_b < 0 || id_b >= KID_COUNT || !ms_total || !launches) return OGG_ERR_ARG;
+  std::vector<std::pair<double, double>> iv;
+  const TimedLaunch* base = nullptr;
   for (auto& t : g_timed) {
-    if (t.id == id_a) a.push_back(&t);
-    else if (t.id == id_b) b.push_back(&t);
+    if (t.id != id_a && t.id != id_b) continue;
+    if (!base) base = &t;
+    OGG_CUDA(cudaEventSynchronize(t.e1));
+    float s = 0.f, e = 0.f;
+    if (&t != base) OGG_CUDA(cudaEventElapsedTime(&s, base->e0, t.e0));   // negative if it started before the base
+    OGG_CUDA(cudaEventElapsedTime(&e, base->e0, t.e1));
+    iv.emplace_back((double)s, (double)e);
   }
-  double tot = 0.0;
-  const size_t n = a.size() > b.size() ? a.size() : b.size();
-  for (size_t k = 0; k < n; ++k) {
-    const TimedLaunch* x = k < a.size() ? a[k] : nullptr;
-    const TimedLaunch* y = k < b.size() ? b[k] : nullptr;
-    if (!x) { x = y; y = nullptr; }
-    OGG_CUDA(cudaEventSynchronize(x->e1));
-    float ea = 0.f, sb = 0.f, eb = 0.f;
-    OGG_CUDA(cudaEventElapsedTime(&ea, x->e0, x->e1));
-    double lo = 0.0, hi = ea;
-    if (y) {
-      OGG_CUDA(cudaEventSynchronize(y->e1));
-      OGG_CUDA(cudaEventElapsedTime(&sb, x->e0, y->e0));   // negative if y started first
-      OGG_CUDA(cudaEventElapsedTime(&eb, x->e0, y->e1));
-      if (sb < lo) lo = sb;
-      if (eb > hi) hi = eb;
-    }
-    tot += hi - lo;
+  std::sort(iv.begin(), iv.end());
+  double tot = 0.0, lo = 0.0, hi = 0.0;
+  bool open = false;
+  for (auto& x : iv) {
+    if (open && x.first <= hi) { if (x.second > hi) hi = x.second; continue; }
+    if (open) tot += hi - lo;
+    lo = x.first; hi = x.second; open = true;
   }
+  if (open) tot += hi - lo;
   *ms_total = tot;
-  *pairs = (long long)n;
+  *launches = (long long)iv.size();
   return OGG_OK;
 }
 int ogg_timing_reset(void) {

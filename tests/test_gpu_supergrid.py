@@ -298,7 +298,7 @@ def test_timing_brackets_and_pair_span(SG):
     (tdp, ndp), (tbp, nbp) = total("dp_hsamples"), total("bipolar_quad_fused")
     span, pairs = ctypes.c_double(), ctypes.c_longlong()
     assert lib.ogg_timing_pair_span(kid["dp_hsamples"], kid["bipolar_quad_fused"], ctypes.byref(span), ctypes.byref(pairs)) == 0
-    assert ndp == nbp == pairs.value == 3 and tdp > 0 and tbp > 0
+    assert ndp == nbp == 3 and pairs.value == 6 and tdp > 0 and tbp > 0
     assert max(tdp, tbp) <= span.value * 1.001 and span.value <= (tdp + tbp) * 1.5 + 1.0
     lib.ogg_timing_reset()
     assert total("dp_hsamples") == (0.0, 0)
