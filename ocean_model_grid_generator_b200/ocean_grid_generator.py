@@ -248,8 +248,9 @@ def mercator_latitudes(Ni, phi_s, phi_n, refineR, shift_equator_to_u_point=True,
         if ensure_nj_even:
             print("  *Fixing this by shifting the y_star[1] ")
             y_star[1] = y_star[1] - 1
-    print("   Generating Mercator grid with phi range: phi_s,phi_n=", phi_mercator(Ni, y_star))
     phi_M = _mercator_law("ogg_phi_mercator", None, Ni / (2 * np.pi), y_first=y_star[0], n=y_star[1] - y_star[0] + 1)  # OGG:336
+    # OGG:335 prints phi_mercator(Ni, y_star): element-wise, so exactly the two end points of phi_M
+    print("   Generating Mercator grid with phi range: phi_s,phi_n=", phi_M[[0, -1]])
     equator_index = numpy.searchsorted(phi_M, 0.0)
     if equator_index == 0:
         raise Exception("   Ooops: Equator is not in the grid")
