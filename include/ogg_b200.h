@@ -11,6 +11,14 @@
  *     with respect to the host unless stated; scratch memory is stream-ordered (cudaMallocAsync);
  *   - return value: 0 on success, OGG_ERR_* below, or OGG_ERR_CUDA - (int)cudaError_t.  Nothing throws.
  * There is no CPU fallback: without a CUDA device every compute entry point returns an error.
+ *
+ * Devices and threads.  Every call works on the CURRENT device of the calling thread (cudaSetDevice), and `stream`
+ * must belong to it; one process may drive several devices (per-device state -- SM count, the shared-memory opt-in
+ * of the fused bipolar kernel, the scratch pool, timing events -- is keyed by device id).  Scratch comes from a
+ * private cudaMemPool per device whose release threshold is "never"; the application's default pool is not touched.
+ * Compute entry points may be called from several host threads at once; the launch counter and the timing brackets
+ * (ogg_launch_count, ogg_timing_*) are process-wide, mutex-guarded, and ogg_timing_get / _pair_span report the
+ * brackets of the current device only.  A call that fails half-way may have queued some of its launches already.
  */
 #ifndef OGG_B200_H_
 #define OGG_B200_H_
@@ -137,6 +145,12 @@ int ogg_sum_strided(const double* a, int64_t n, int64_t stride, double* out, voi
  * checksum, additive over row-slabs -- array-level parity where the arrays are too large to copy out; stands where the
  * reference prints chksum(x, label) (OGG:19-30, sha256 of the host array) */
 int ogg_checksum_accumulate(const double* a, int64_t n, uint64_t* acc, void* stream);
+
+/* ---- file output (write_nc, OGG:773-829) ---------------------------------------------------------------------
+ * out[e] = byte-reversed in[e] for n 8-byte elements: the big-endian doubles the netCDF classic format stores.  `in` is
+ * a device pointer; `out` is a device pointer OR pinned host memory (cudaHostAlloc: mapped under unified addressing), in
+ * which case the kernel's stores are the device->host transfer. */
+int ogg_bswap64(const void* in, void* out, int64_t n, void* stream);
 
 /* ---- launch accounting (bench.py: gpu_launches and per-kernel CUDA-event durations) ---------------------------------- */
 /* kernels launched by this library since it was loaded */

@@ -47,6 +47,7 @@ SIGNATURES = {
     "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _dp, _dp, _vp],
     "ogg_sum_strided": [_dp, _i64, _i64, _dp, _vp],
     "ogg_checksum_accumulate": [_dp, _i64, _vp, _vp],
+    "ogg_bswap64": [_vp, _vp, _i64, _vp],
     "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
     "ogg_selftest_divsqrt": [_i64, ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)],
     "ogg_launch_count": [], "ogg_timing_enable": [_int], "ogg_timing_reset": [], "ogg_timing_kernels": [],

@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <utility>
 #include <vector>
 
@@ -33,38 +34,57 @@ using i64 = long long;
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 static inline unsigned cdiv_u(i64 a, i64 b) { return static_cast<unsigned>((a + b - 1) / b); }
 
-static int g_num_sms = 0;
+// Per-device state (one process may drive several devices): everything cached about "the device" is keyed
+// by the current device id.
+constexpr int kMaxDevices = 64;
+static inline int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 0;
+  return dev;
+}
 static int num_sms() {
-  if (g_num_sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-    if (cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) g_num_sms = 148;
+  static int sms[kMaxDevices] = {0};
+  const int dev = current_device();
+  if (sms[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    sms[dev] = n;
   }
-  return g_num_sms;
+  return sms[dev];
 }
 
-// stream-ordered scratch.  The default pool would hand its memory back to the driver at every synchronisation;
-// keep it, so that steady-state steps never touch the physical allocator.
-static void keep_pool_memory() {
-  static int done_for = -1;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev == done_for) return;
-  cudaMemPool_t pool;
-  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+// stream-ordered scratch from a PRIVATE pool per device (the host application's default pool is left alone) whose
+// release threshold is "never": steady-state steps do not reach the physical allocator.
+static std::mutex g_pool_mutex;
+static cudaMemPool_t scratch_pool() {
+  static cudaMemPool_t pools[kMaxDevices] = {nullptr};
+  const int dev = current_device();
+  std::lock_guard<std::mutex> lock(g_pool_mutex);
+  if (!pools[dev]) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    cudaMemPool_t pool = nullptr;
+    if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     unsigned long long thr = ~0ull;
     cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    pools[dev] = pool;
   }
-  done_for = dev;
+  return pools[dev];
 }
 struct Scratch {
   cudaStream_t st;
+  cudaMemPool_t pool;
   void* ptrs[16];
   int n = 0;
-  explicit Scratch(cudaStream_t s) : st(s) { keep_pool_memory(); }
+  explicit Scratch(cudaStream_t s) : st(s), pool(scratch_pool()) {}
   template <typename T>
   cudaError_t get(T** p, size_t count) {
     void* q = nullptr;
-    cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) + 16, st);
+    cudaError_t e = pool ? cudaMallocFromPoolAsync(&q, count * sizeof(T) + 16, pool, st)
+                         : cudaMallocAsync(&q, count * sizeof(T) + 16, st);
     if (e != cudaSuccess) return e;
     ptrs[n++] = q;
     *p = static_cast<T*>(q);
@@ -88,29 +108,43 @@ static const char* const kKernelNames[KID_COUNT] = {
     "elementwise", "band_tables", "band_fill", "midas", "angle_x", "bipolar_projection", "bipolar_tables", "bipolar_mesh",
     "bipolar_samples", "bipolar_quad_fused", "sample_index", "quad_cells", "dp_setup", "dp_tables", "dp_raw", "monotonic_bounding", "dp_hsamples",
     "reduce"};
+// Thread safety: the counters and the list of bracketed launches are shared by all host threads and devices of the
+// process and guarded by one mutex; whether the CURRENT launch is bracketed is per thread.
+static std::mutex g_timing_mutex;
 static long long g_launches = 0;
 static int g_timing = 0;         // 0 off, 1 every launch, 2 only the heavy kernel classes (caps + band fill)
-static bool g_timed_this = false;
-struct TimedLaunch { int id; cudaEvent_t e0, e1; };
+struct TimedLaunch { int id, dev; cudaEvent_t e0, e1; bool ended; };   // events belong to the device they were created on
 static std::vector<TimedLaunch> g_timed;
-static std::vector<cudaEvent_t> g_event_pool;
-static cudaEvent_t take_event() {
-  if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+static std::vector<cudaEvent_t> g_event_pool[kMaxDevices];
+static thread_local long long t_timed_index = -1;   // index into g_timed of this thread's open bracket
+static cudaEvent_t take_event(int dev) {   // g_timing_mutex held
+  auto& pool = g_event_pool[dev];
+  if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
   cudaEvent_t e;
   cudaEventCreate(&e);
   return e;
 }
 static inline void launch_begin(int id, cudaStream_t st) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
   ++g_launches;
-  g_timed_this = g_timing == 1 || (g_timing == 2 && (id == KID_DP_HSAMPLES || id == KID_BP_QUAD || id == KID_BAND_FILL));
-  if (g_timed_this) {
-    TimedLaunch t{id, take_event(), take_event()};
+  t_timed_index = -1;
+  if (g_timing == 1 || (g_timing == 2 && (id == KID_DP_HSAMPLES || id == KID_BP_QUAD || id == KID_BAND_FILL))) {
+    const int dev = current_device();
+    TimedLaunch t{id, dev, take_event(dev), take_event(dev), false};
     cudaEventRecord(t.e0, st);
     g_timed.push_back(t);
+    t_timed_index = (long long)g_timed.size() - 1;
   }
 }
+// an entry whose launch_end never ran (an error return in between) stays !ended and is skipped by the readers
 static inline void launch_end(cudaStream_t st) {
-  if (g_timed_this) cudaEventRecord(g_timed.back().e1, st);
+  if (t_timed_index < 0) return;
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  if (t_timed_index < (long long)g_timed.size()) {
+    cudaEventRecord(g_timed[t_timed_index].e1, st);
+    g_timed[t_timed_index].ended = true;
+  }
+  t_timed_index = -1;
 }
 template <typename K, typename... A>
 static inline void launch_cfg(cudaStream_t st, dim3 g, dim3 b, K k, A... a) {
@@ -1295,6 +1329,18 @@ __global__ void __launch_bounds__(kRedThreads) k_checksum(const double* __restri
   if ((threadIdx.x & 31u) == 0u) atomicAdd(acc, v);   // integer addition: the result does not depend on the order
 }
 
+// Byte-order reversal of 8-byte elements (the netCDF classic format is big-endian): `out` may be device memory or
+// pinned host memory mapped into the device's address space -- the stores then cross PCIe directly, which replaces the
+// host-side astype(">f8") pass AND the separate device->host copy of write_nc (OGG:773-829).
+__global__ void __launch_bounds__(256) k_bswap64(const unsigned long long* __restrict__ in, unsigned long long* __restrict__ out,
+                                                 i64 n) {
+  for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
+    const unsigned long long v = in[e];
+    const unsigned lo = (unsigned)v, hi = (unsigned)(v >> 32);
+    out[e] = ((unsigned long long)__byte_perm(lo, 0u, 0x0123) << 32) | (unsigned long long)__byte_perm(hi, 0u, 0x0123);
+  }
+}
+
 // FP64 issue-rate probe: 8 independent chains of dependent (mul, add) pairs
 __global__ void __launch_bounds__(256) k_fp64_rate(i64 iters, double seed, double* __restrict__ sink) {
   double a[8];
@@ -1351,10 +1397,11 @@ static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 n
   constexpr int TR = kBpTileRows, TC = kBpTileCols;
   static_assert(TR * TC <= 256, "one thread per cell");
   constexpr size_t smem = sizeof(double) * 2 * ((N - 1) * TR + 1) * ((N - 1) * (TC + 1));
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[kMaxDevices] = {false};   // the opt-in to > 48 KB of dynamic shared memory is per device
+  const int dev = current_device();
+  if (!configured[dev]) {
     OGG_CUDA(cudaFuncSetAttribute(k_bp_quad_fused<N, TR, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured[dev] = true;
   }
   const dim3 g(cdiv_u(nx, TC), cdiv_u(ncr, TR));
   launch_begin(KID_BP_QUAD, st);
@@ -1391,8 +1438,12 @@ int ogg_device_count(void) {
   return n;
 }
 
-long long ogg_launch_count(void) { return g_launches; }
+long long ogg_launch_count(void) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  return g_launches;
+}
 int ogg_timing_enable(int on) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
   g_timing = on < 0 ? 0 : (on > 2 ? 1 : on);
   return OGG_OK;
 }
@@ -1402,10 +1453,12 @@ int ogg_timing_enable(int on) {
 // chunked on large grids, a rank may hold several slabs per step).
 int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* launches) {
   if (id_a < 0 || id_a >= KID_COUNT || id_b < 0 || id_b >= KID_COUNT || !ms_total || !launches) return OGG_ERR_ARG;
+  const int dev = current_device();   // brackets of the current device only (event times of two devices do not compare)
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
   std::vector<std::pair<double, double>> iv;
   const TimedLaunch* base = nullptr;
   for (auto& t : g_timed) {
-    if (t.id != id_a && t.id != id_b) continue;
+    if (!t.ended || t.dev != dev || (t.id != id_a && t.id != id_b)) continue;
     if (!base) base = &t;
     OGG_CUDA(cudaEventSynchronize(t.e1));
     float s = 0.f, e = 0.f;
@@ -1427,7 +1480,8 @@ int ogg_timing_pair_span(int id_a, int id_b, double* ms_total, long long* launch
   return OGG_OK;
 }
 int ogg_timing_reset(void) {
-  for (auto& t : g_timed) { g_event_pool.push_back(t.e0); g_event_pool.push_back(t.e1); }
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  for (auto& t : g_timed) { g_event_pool[t.dev].push_back(t.e0); g_event_pool[t.dev].push_back(t.e1); }
   g_timed.clear();
   return OGG_OK;
 }
@@ -1435,10 +1489,12 @@ int ogg_timing_kernels(void) { return KID_COUNT; }
 const char* ogg_timing_name(int id) { return (id >= 0 && id < KID_COUNT) ? kKernelNames[id] : ""; }
 int ogg_timing_get(int id, double* ms_total, long long* launches) {
   if (id < 0 || id >= KID_COUNT || !ms_total || !launches) return OGG_ERR_ARG;
+  const int dev = current_device();
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
   double tot = 0.0;
   long long n = 0;
   for (auto& t : g_timed) {
-    if (t.id != id) continue;
+    if (!t.ended || t.dev != dev || t.id != id) continue;
     OGG_CUDA(cudaEventSynchronize(t.e1));
     float ms = 0.f;
     OGG_CUDA(cudaEventElapsedTime(&ms, t.e0, t.e1));
@@ -1910,6 +1966,15 @@ int ogg_checksum_accumulate(const double* a, int64_t n, uint64_t* acc, void* str
   const i64 want = (n + kRedThreads - 1) / kRedThreads;
   const unsigned g = (unsigned)(want < (i64)num_sms() * 8 ? want : (i64)num_sms() * 8);
   OGG_LAUNCH(KID_REDUCE, (k_checksum), (g, kRedThreads), (st), a, (i64)n, reinterpret_cast<unsigned long long*>(acc));
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
+int ogg_bswap64(const void* in, void* out, int64_t n, void* stream) {
+  if (n < 0 || (n > 0 && (!in || !out))) return OGG_ERR_ARG;
+  if (n == 0) return OGG_OK;
+  OGG_LAUNCH(KID_ELEMENTWISE, (k_bswap64), (flat_grid(n, 16), 256), (S(stream)), static_cast<const unsigned long long*>(in),
+             static_cast<unsigned long long*>(out), (i64)n);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }

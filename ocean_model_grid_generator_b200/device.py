@@ -39,11 +39,23 @@ def to_host(t):
     return t.detach().cpu().numpy()
 
 
+def _check(t):
+    # the C ABI takes raw pointers + logical shapes: a strided view would be read / written with the wrong strides
+    if not t.is_contiguous():
+        raise _cabi.OggError("a non-contiguous tensor reached the C ABI; pass .contiguous() data")
+    if t.dtype not in (torch.float64, torch.int64):
+        raise _cabi.OggError("the C ABI takes 8-byte elements, got %s" % t.dtype)
+
+
 def ptr(t):
-    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    if t is None:
+        return None
+    _check(t)
+    return ctypes.c_void_p(t.data_ptr())
 
 
 def ptr_off(t, elem_offset):
+    _check(t)
     return ctypes.c_void_p(t.data_ptr() + 8 * int(elem_offset))
 
 

@@ -89,6 +89,11 @@ def write_supergrid(fnam, x, y, dx, dy, area, angle_dx, global_attrs=None, forma
             if vtype == NC_CHAR:
                 raw = data.tobytes()
                 f.write(raw + b"\x00" * _pad4(len(raw)))
+            elif hasattr(data, "bigendian_chunks"):
+                # a producer of ready-made big-endian bytes (the device path: byte order reversed on the GPU, written
+                # straight into pinned host staging buffers): nothing is converted or copied on the host
+                for chunk in data.bigendian_chunks():
+                    f.write(chunk)
             else:
                 a = np.ascontiguousarray(data, dtype=np.float64)
                 step = max(1, (1 << 24) // max(1, a.shape[1]))

@@ -365,7 +365,12 @@ def displacedPoleCap_projection(lon_grid, lat_grid, z_0, r_joint):
 def monotonic_bounding(x, x_0):
     """OGG:470-475; in place, like the reference."""
     if _dev.is_dev(x):
-        _cabi.call("ogg_monotonic_bounding", _dev.ptr(x), x.shape[0], x.shape[1], float(x_0), _dev.stream())
+        if x.is_contiguous() and x.dtype == _dev.torch.float64:
+            _cabi.call("ogg_monotonic_bounding", _dev.ptr(x), x.shape[0], x.shape[1], float(x_0), _dev.stream())
+        else:   # a strided view (e.g. a column slice): scan a contiguous copy, write it back through the view
+            t = _dev.to_dev(x).clone()
+            _cabi.call("ogg_monotonic_bounding", _dev.ptr(t), t.shape[0], t.shape[1], float(x_0), _dev.stream())
+            x.copy_(t)
         return x
     t = _dev.to_dev(x)
     _cabi.call("ogg_monotonic_bounding", _dev.ptr(t), t.shape[0], t.shape[1], float(x_0), _dev.stream())
@@ -543,24 +548,36 @@ def metrics_error(dx_, dy_, area_, Ni, lat1, lat2=90, Re=_default_Re, bipolar=Fa
         r = r % a.shape[0]
         return device_sum(a, n=a.shape[1], stride=1, offset=r * a.shape[1])
 
-    exact_area = 2 * np.pi * (Re ** 2) * numpy.abs(np.sin(lat2 * PI_180) - np.sin(lat1 * PI_180))
-    exact_lat_arc_length = numpy.abs(lat2 - lat1) * PI_180 * Re
-    exact_lon_arc_length = np.cos(lat1 * PI_180) * 2 * np.pi * Re
-    grid_lat_arc_length = col_sum(dy_, Ni // 4)
-    grid_lon_arc_length = row_sum(dx_, 0)
-    if lat1 > lat2:
-        grid_lon_arc_length = row_sum(dx_, -1)
-    if bipolar:
-        grid_lon_arc_length2 = row_sum(dx_, -1)
-        lon_arc2_error = 100 * (grid_lon_arc_length2 / 4 - exact_lat_arc_length) / exact_lat_arc_length
-    area_error = 100 * (device_sum(area_) - exact_area) / exact_area
-    lat_arc_error = 100 * (grid_lat_arc_length - exact_lat_arc_length) / exact_lat_arc_length
-    lon_arc_error = 100 * (grid_lon_arc_length - exact_lon_arc_length) / exact_lon_arc_length
+    sums = {"area": device_sum(area_), "dy_quarter": col_sum(dy_, Ni // 4), "dx_first": row_sum(dx_, 0)}
+    if lat1 > lat2 or bipolar:
+        sums["dx_last"] = row_sum(dx_, -1)
     if displaced_pole != -999:
         antipole = displaced_pole + Ni // 2
         if displaced_pole > Ni // 2:
             antipole = displaced_pole - Ni // 2
-        grid_lat_arc_length = col_sum(dy_, displaced_pole) + col_sum(dy_, antipole)
+        sums["dy_pole"], sums["dy_antipole"] = col_sum(dy_, displaced_pole), col_sum(dy_, antipole)
+    return metrics_error_from_sums(sums, lat1, lat2, Re, bipolar, displaced_pole, excluded_fraction)
+
+
+def metrics_error_from_sums(sums, lat1, lat2=90, Re=_default_Re, bipolar=False, displaced_pole=-999, excluded_fraction=None):
+    """The arithmetic of OGG:743-770 on the sums OGG:747-756 takes from the arrays: sums = {"area": sum(area_),
+    "dy_quarter": sum(dy_[:, Ni//4]), "dx_first": sum(dx_[0]), "dx_last": sum(dx_[-1]), "dy_pole" / "dy_antipole":
+    sum(dy_[:, displaced_pole]) / sum(dy_[:, antipole])}.  Row-slabs / row chunks add their partial sums first."""
+    exact_area = 2 * np.pi * (Re ** 2) * numpy.abs(np.sin(lat2 * PI_180) - np.sin(lat1 * PI_180))
+    exact_lat_arc_length = numpy.abs(lat2 - lat1) * PI_180 * Re
+    exact_lon_arc_length = np.cos(lat1 * PI_180) * 2 * np.pi * Re
+    grid_lat_arc_length = sums["dy_quarter"]
+    grid_lon_arc_length = sums["dx_first"]
+    if lat1 > lat2:
+        grid_lon_arc_length = sums["dx_last"]
+    if bipolar:
+        grid_lon_arc_length2 = sums["dx_last"]
+        lon_arc2_error = 100 * (grid_lon_arc_length2 / 4 - exact_lat_arc_length) / exact_lat_arc_length
+    area_error = 100 * (sums["area"] - exact_area) / exact_area
+    lat_arc_error = 100 * (grid_lat_arc_length - exact_lat_arc_length) / exact_lat_arc_length
+    lon_arc_error = 100 * (grid_lon_arc_length - exact_lon_arc_length) / exact_lon_arc_length
+    if displaced_pole != -999:
+        grid_lat_arc_length = sums["dy_pole"] + sums["dy_antipole"]
         lat_arc_error = 100 * (grid_lat_arc_length - 2.0 * exact_lat_arc_length) / exact_lat_arc_length
     if excluded_fraction:
         print("   Cannot estimate area and dy accuracies with excluded_fraction (doughnut)! ")
@@ -569,24 +586,96 @@ def metrics_error(dx_, dy_, area_, Ni, lat1, lat2=90, Re=_default_Re, bipolar=Fa
     return area_error, lat_arc_error, lon_arc_error
 
 
+def displacedPoleCap_metrics_sums(order, nx, ny, lon0, lat0, lon_dp, r_dp, displaced_pole, Re=_default_Re, max_rows=64):
+    """The sums metrics_error (OGG:747-756, 763-765) takes from displacedPoleCap_metrics_quad's arrays over the WHOLE cap,
+    accumulated over chunks of `max_rows` cell rows in bounded scratch -- no array of the full cap is ever held.  This is
+    how main()'s `CHECK_metrics_hquad` line for the southern cap (OGG:1170-1174) is evaluated when only the rows kept
+    after the doughnut cut are generated."""
+    nx, ny = int(nx), int(ny)
+    antipole = displaced_pole + nx // 2
+    if displaced_pole > nx // 2:
+        antipole = displaced_pole - nx // 2
+    rows = min(int(max_rows), ny)
+    dxq, dyq, daq = _dev.empty(rows + 1, nx), _dev.empty(rows, nx + 1), _dev.empty(rows, nx)
+    sums = {"area": 0.0, "dy_quarter": 0.0, "dx_first": 0.0, "dx_last": 0.0, "dy_pole": 0.0, "dy_antipole": 0.0}
+    for j0 in range(0, ny, rows):
+        j1 = min(ny, j0 + rows)
+        n = j1 - j0
+        _cabi.call("ogg_dp_metrics_quad", int(order), nx, ny, j0, j1, float(lon0), float(lat0), float(lon_dp), float(r_dp),
+                   float(Re), 0, _dev.ptr(dxq), _dev.ptr(dyq), _dev.ptr(daq), _dev.stream())
+        sums["area"] += device_sum(daq, n=n * nx)
+        for key, col in (("dy_quarter", nx // 4), ("dy_pole", displaced_pole), ("dy_antipole", antipole)):
+            sums[key] += device_sum(dyq, n=n, stride=nx + 1, offset=col)
+        if j0 == 0:
+            sums["dx_first"] = device_sum(dxq, n=nx)
+        if j1 == ny:
+            sums["dx_last"] = device_sum(dxq, n=nx, offset=n * nx)
+    return sums
+
+
 # --------------------------------------------------------------------------------------------------
 # file output (OGG:773-829)
 # --------------------------------------------------------------------------------------------------
+_STAGING = {}
+
+
+class _DeviceVariable(object):
+    """One output variable resident in HBM, handed to the CDF-2 writer as a producer of big-endian bytes.
+
+    The byte order is reversed on the GPU (ogg_bswap64) with the kernel's stores landing directly in pinned host memory,
+    in chunks through two staging buffers: the device fills one while the host writes the other to the file.  Replaces
+    the reference path's host copy + netCDF-C's per-element byte swap (write_nc, OGG:795-821)."""
+    CHUNK = 1 << 23     # elements per staging buffer (64 MiB)
+
+    def __init__(self, t):
+        self.t = t.contiguous()
+        self.shape = tuple(t.shape)
+
+    def bigendian_chunks(self):
+        import torch
+        flat = self.t.reshape(-1)
+        n = flat.numel()
+        key = torch.cuda.current_device()
+        if key not in _STAGING:
+            _STAGING[key] = ([torch.empty(self.CHUNK, dtype=torch.int64, pin_memory=True) for _ in range(2)],
+                             [torch.cuda.Event() for _ in range(2)], torch.cuda.Stream())
+        bufs, events, side = _STAGING[key]
+        side.wait_stream(torch.cuda.current_stream())      # the producers of self.t
+        starts = list(range(0, n, self.CHUNK))
+
+        def launch(k):
+            e0 = starts[k]
+            m = min(self.CHUNK, n - e0)
+            with torch.cuda.stream(side):
+                _cabi.call("ogg_bswap64", _dev.ptr_off(flat, e0), _dev.ptr(bufs[k % 2]), m, _dev.stream())
+                events[k % 2].record(side)
+            return m
+
+        sizes = {0: launch(0)} if starts else {}
+        for k in range(len(starts)):
+            if k + 1 < len(starts):
+                sizes[k + 1] = launch(k + 1)    # the other buffer: its previous contents were written out one step ago
+            events[k % 2].synchronize()
+            yield memoryview(bufs[k % 2].numpy()).cast("B")[:8 * sizes[k]]
+
+
 def write_nc(x, y, dx, dy, area, angle_dx, axis_units="degrees", fnam=None, format="NETCDF3_64BIT", description=None,
              history=None, source=None, no_changing_meta=None, debug=False):
-    """Same variables, dimensions, attributes and CDF-2 container as the reference's netCDF4 call sequence."""
+    """Same variables, dimensions, attributes and CDF-2 container as the reference's netCDF4 call sequence
+    (OGG:773-829).  Device tensors are streamed out big-endian by the GPU (see _DeviceVariable); numpy arrays are
+    converted on the host."""
     if fnam is None:
         fnam = "supergrid.nc"
-    arrs = [(_dev.to_host(a) if _dev.is_dev(a) else numpy.asarray(a)) for a in (x, y, dx, dy, area, angle_dx)]
-    x, y, dx, dy, area, angle_dx = arrs
+    arrs = [x, y, dx, dy, area, angle_dx]
     if debug:
         for a, lbl in zip(arrs, ("x", "y", "dx", "dy", "area", "angle_dx")):
-            chksum(a, lbl)
-    print("   Writing netcdf file with ny,nx= ", area.shape[0], area.shape[1])
+            chksum(_dev.to_host(a) if _dev.is_dev(a) else numpy.asarray(a), lbl)
+    arrs = [_DeviceVariable(a) if _dev.is_dev(a) else numpy.asarray(a) for a in arrs]
+    print("   Writing netcdf file with ny,nx= ", arrs[4].shape[0], arrs[4].shape[1])
     attrs = None
     if not no_changing_meta:
         attrs = [("history", history), ("description", description), ("source", source)]
-    _netcdf3.write_supergrid(fnam, x, y, dx, dy, area, angle_dx, attrs, format=format)
+    _netcdf3.write_supergrid(fnam, *arrs, attrs, format=format)
 
 
 def usage():

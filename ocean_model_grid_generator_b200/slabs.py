@@ -40,13 +40,21 @@ def exchange_halo(x, y, group=None):
     rank, world = _world(group)
     if world == 1:
         return None
-    if x.shape != y.shape or x.dim() != 2:
-        raise Exception("Input arrays do not have the same shape!")
-    nxp = x.shape[1]
+    # Validate on every rank BEFORE any point-to-point operation is posted: a rank that raised on its own would leave
+    # its neighbours blocked in their send / receive.  One tiny all-reduce (min of "my arguments are fine", and the
+    # row length, which must agree across ranks).
+    good = x.dim() == 2 and tuple(x.shape) == tuple(y.shape) and (rank == 0 or x.shape[0] >= 1)
+    nxp = int(x.shape[1]) if x.dim() == 2 else -1
+    check = torch.tensor([1 if good else 0, nxp, -nxp], dtype=torch.int64, device=x.device)
+    dist.all_reduce(check, op=dist.ReduceOp.MIN, group=group)
+    if int(check[0]) == 0:
+        if x.dim() != 2 or tuple(x.shape) != tuple(y.shape):
+            raise Exception("Input arrays do not have the same shape!")
+        raise Exception("exchange_halo: a rank owns no mesh row to send or passed mismatched arrays (this rank: %d)" % rank)
+    if int(check[1]) != -int(check[2]):
+        raise Exception("exchange_halo: the ranks' meshes differ in the number of columns")
     ops, recv = [], None
     if rank > 0:
-        if x.shape[0] < 1:
-            raise Exception("exchange_halo: rank %d owns no mesh row to send" % rank)
         send = torch.stack((x[0], y[0])).contiguous()
         ops.append(dist.P2POp(dist.isend, send, dist.get_global_rank(group, rank - 1) if group else rank - 1, group))
     if rank < world - 1:

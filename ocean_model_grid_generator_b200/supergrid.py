@@ -38,6 +38,11 @@ class Piece(object):
     def cut(self, n):
         self.row0 += int(n)
 
+    def copy(self):
+        q = Piece(self.name, self.kind, self.rows_full, **self.p)
+        q.row0 = self.row0
+        return q
+
 
 class Plan(object):
     def __init__(self, Ni, pieces, skip_metrics, info):
@@ -82,6 +87,9 @@ def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfr
     if refineR == 1 and enhanced_equatorial:
         phi_s_Merc, phi_n_Merc = -77.8, 60.0                                       # OGG:999-1001
     info = {"lon0": lon0, "doughnut": doughnut}
+    # every sub-grid as main() first generates it (before the doughnut / parity / south cuts): what its CHECK_metrics line
+    # is evaluated on (OGG:1016, 1069, 1111, 1156, 1172) and, for Merc / BP / SO, what --write_subgrid_files writes
+    as_generated = info["as_generated"] = {}
     lam1d = lon0 + numpy.arange(Ni + 1) * lenlon / float(Ni)                       # OGG:431, :834 (same law)
 
     merc = bp = so = sc = None
@@ -91,6 +99,7 @@ def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfr
         if phiM.shape[0] % 2 == 0 and ensure_nj_even:                               # OGG:434-437
             phiM = phiM[1:]
         merc = Piece("Merc", "band", phiM.shape[0], lam=lam1d, phi=phiM)
+        as_generated["Merc"] = merc.copy()
         DeltaPhiMerc_so = phiM[1] - phiM[0]                                         # OGG:1024-1025
         DeltaPhiMerc_no = phiM[-1] - phiM[-2]
         lat0_bp = phiM[-1]                                                          # OGG:1030
@@ -109,6 +118,7 @@ def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfr
             Nj_ncap -= 1
         bp = Piece("BP", "bipolar", Nj_ncap + 1, Nj=Nj_ncap, lat0_bp=float(lat0_bp), lon_bp=lon0,
                    rp=ogg.bipolar_rp(lat0_bp))
+        as_generated["BP"] = bp.copy()
     # Southern Ocean band (OGG:1080-1116)
     lat0_SO = -78.0
     if south_ocean_lower_lat > -90:
@@ -129,6 +139,7 @@ def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfr
     if Nj_SO != 0 and _has(grids, "so"):
         lamSO, phiSO = ogg.latlon_vectors(Ni, Nj_SO, lon0, lenlon, lat0_SO, lenlat_SO, ensure_nj_even)
         so = Piece("SO", "band", phiSO.shape[0], lam=lamSO, phi=phiSO)
+        as_generated["SO"] = so.copy()
     if so is None:
         raise Exception("the Southern Ocean sub-grid is required: the reference reads phiSO at OGG:1122")
     # South cap (OGG:1122-1195)
@@ -145,18 +156,22 @@ def plan_supergrid(inverse_resolution, r_dp=0.0, lon_dp=80.0, lat_dp=-99.0, exfr
             Nj_scap = int(fullArc / deltaPhiSO)
             lamSC, phiSC = ogg.latlon_vectors(Ni, Nj_scap, lon0, lenlon, -90.0, 90 + lat0_SO, ensure_nj_even)
             sc = Piece("SC", "band", phiSC.shape[0], lam=lamSC, phi=phiSC, regular=True)
+            as_generated["SC"] = sc.copy()
         else:                                                                       # displaced pole, OGG:1158-1195
             if lat_dp > -90:
                 r_dp = float(np.tan((90 + lat_dp) * PI_180) / np.tan((90 + lat0_SC) * PI_180))   # OGG:1160
                 info["r_dp"] = r_dp
             sc = Piece("SC", "dp", Nj_scap + 1, Ni=Ni, Nj=Nj_scap, lon0=lon0, lat0=float(lat0_SC), lon_dp=float(lon_dp),
                        r_dp=float(r_dp))
+            as_generated["SC"] = sc.copy()
             if doughnut != 0.0:
                 jmin = numpy.ceil(doughnut * Nj_scap)                               # OGG:1178-1180
                 sc.cut(int(jmin + numpy.mod(jmin, 2)))
             if sc.rows % 2 == 0 and ensure_nj_even:                                 # OGG:1188-1195
                 sc.cut(1)
     info["lat0_SC"] = lat0_SC
+    if sc is not None:
+        info["SC_file_piece"] = sc.copy()       # what --write_subgrid_files writes for SC (OGG:1227-1229): before the south cut
 
     # South cut (OGG:1270-1313)
     cut, jcut = False, 0
@@ -422,30 +437,65 @@ def generate(host=None, **kwargs):
 
 
 # --------------------------------------------------------------------------------------------------
-# stand-alone sub-grids (for --write_subgrid_files and the CHECK_metrics lines)
+# main(): the CHECK_metrics self-check lines, --write_subgrid_files, the stitched file
 # --------------------------------------------------------------------------------------------------
 def build_piece_standalone(plan, piece):
     sub = Plan(plan.Ni, [piece], plan.skip_metrics, plan.info)
     return build_supergrid(sub)
 
 
-def _check_lines(plan, piece, sg):
-    a = sg.arrays()
-    if plan.skip_metrics:
+def _stitched_views(plan, sg, name):
+    """(dx, dy, area) of sub-grid `name` as row ranges of the stitched arrays, or None when the stitched grid does not
+    hold what metrics_error reads from that sub-grid as main() generated it (rows cut away, or its own top dx row)."""
+    for piece, off in zip(plan.pieces, plan.offsets()):
+        if piece.name != name:
+            continue
+        full = plan.info["as_generated"][name]
+        if piece.row0 != 0 or piece.rows_full != full.rows_full or piece.kind == "dp":
+            return None
+        if piece.kind == "band" and piece.p.get("regular"):
+            return None                      # OGG:1157 reads the regular cap's OWN top dx row, which the join drops
+        closes = piece is plan.pieces[-1]
+        if piece.kind == "bipolar" and not closes:
+            return None
+        n = piece.rows - 1
+        return sg.dx[off:off + n + 1], sg.dy[off:off + n], sg.area[off:off + n]
+    return None
+
+
+def check_line(plan, name, sg=None, standalone=None):
+    """Prints the reference's self-check line of one sub-grid (OGG:1016-1017, 1069-1070, 1111-1112, 1156-1157,
+    1172-1174), evaluated on the sub-grid as main() first generates it.  The sums come from the stitched arrays where
+    they hold those rows, from a stand-alone build of the sub-grid (`standalone`, or made here) otherwise, and for the
+    displaced-pole cap -- whose rows inside the doughnut are never stored -- from a chunked reduction over the whole cap."""
+    full = plan.info["as_generated"].get(name)
+    if full is None or plan.skip_metrics:
         return
-    if piece.kind == "band":
-        phi = piece.p["phi"][piece.row0:]
-        lat1, lat2 = phi[0], phi[-1]
-        if piece.p.get("regular"):
-            lat1, lat2 = phi[-1], phi[0]                                            # OGG:1157
-        label = "CHECK_metrics" if piece.name == "Merc" else "CHECK_metrics_MIDAS"
-        print("   %s: %% errors in (area, lat arc, lon arc)" % label,
-              ogg.metrics_error(a["dx"], a["dy"], a["area"], plan.Ni, lat1, lat2))
-    elif piece.kind == "bipolar":
+    if full.kind == "dp":
+        p = full.p
+        poles_i = int(plan.Ni * numpy.mod(p["lon_dp"] - p["lon0"], 360) / 360.0)                     # OGG:1171
+        sums = ogg.displacedPoleCap_metrics_sums(4, plan.Ni, p["Nj"], p["lon0"], p["lat0"], p["lon_dp"], p["r_dp"], poles_i)
+        err = ogg.metrics_error_from_sums(sums, p["lat0"], -90.0, displaced_pole=poles_i,
+                                          excluded_fraction=plan.info["doughnut"])
+        print("   CHECK_metrics_hquad: % errors in (area, lat arc, lon arc)", err)
+        return
+    views = _stitched_views(plan, sg, name) if sg is not None else None
+    if views is None:
+        if standalone is None:
+            standalone = build_piece_standalone(plan, full)
+        a = standalone.arrays()
+        views = a["dx"], a["dy"], a["area"]
+    dx_, dy_, area_ = views
+    if full.kind == "bipolar":
         print("   CHECK_metrics_hquad: % errors in (area, lat arc, lon arc1, lon arc2)",
-              ogg.metrics_error(a["dx"], a["dy"], a["area"], plan.Ni, piece.p["lat0_bp"], 90.0, bipolar=True))
-    else:
-        print("   CHECK_metrics_hquad: not evaluated (only the rows kept after the doughnut cut are generated)")
+              ogg.metrics_error(dx_, dy_, area_, plan.Ni, full.p["lat0_bp"], 90.0, bipolar=True))
+        return
+    phi = full.p["phi"]
+    lat1, lat2 = phi[0], phi[-1]
+    if full.p.get("regular"):
+        lat1, lat2 = phi[-1], phi[0]                                                # OGG:1157
+    label = "CHECK_metrics" if name == "Merc" else "CHECK_metrics_MIDAS"
+    print("   %s: %% errors in (area, lat arc, lon arc)" % label, ogg.metrics_error(dx_, dy_, area_, plan.Ni, lat1, lat2))
 
 
 def run_main(args):
@@ -469,20 +519,31 @@ def run_main(args):
                                                              "write_subgrid_files", "reproduce_MIDAS_grids")}
     plan = plan_supergrid(**plan_args)
     info = plan.info
-    if args["write_subgrid_files"]:
-        for piece in plan.pieces:
-            sg = build_piece_standalone(plan, piece)
-            _check_lines(plan, piece, sg)
-            a = sg.arrays()
-            ogg.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], axis_units="degrees",
-                         fnam=gridfilename + piece.name + ".nc", description=desc, history=hist, source=source,
-                         debug=debug)
     if len(plan.pieces) < 2:
         raise Exception("nothing to stitch: the reference needs at least two adjoining sub-grids (OGG:1237-1247)")
+    sg = build_supergrid(plan)               # one in-place build of the stitched grid; everything below reads it
+    # Per sub-grid, in main()'s order (Mercator, bipolar cap, Southern Ocean, southern cap): the CHECK_metrics line and,
+    # with --write_subgrid_files, its own file.  A sub-grid's file holds its OWN closing vertex row (which the join
+    # drops) and the rows main() had at that point -- Mercator / bipolar / Southern Ocean as generated (OGG:1020, 1074,
+    # 1115: before any south cut), the southern cap after the doughnut cut (OGG:1228) -- so the files come from
+    # stand-alone builds, which then also serve the check lines.
+    for name in ("Merc", "BP", "SO", "SC"):
+        if name not in info["as_generated"]:
+            continue
+        file_piece = info.get("SC_file_piece") if name == "SC" else info["as_generated"][name]
+        standalone = None
+        if args["write_subgrid_files"]:
+            standalone = build_piece_standalone(plan, file_piece)
+        full_build = standalone if (standalone is not None and file_piece.row0 == 0) else None
+        check_line(plan, name, sg, full_build)
+        if standalone is not None:
+            a = standalone.arrays()
+            ogg.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], axis_units="degrees",
+                         fnam=gridfilename + name + ".nc", description=desc, history=hist, source=source, debug=debug)
+            del standalone, a
     print("Stitching the grids together...")
-    sg = build_supergrid(plan)
     a = sg.arrays()
-    ycol = _dev.to_host(a["y"][:, plan.Ni // 4])
+    ycol = _dev.to_host(a["y"][:, plan.Ni // 4].contiguous())
     if info["hasBP"]:
         dy3_ = numpy.roll(ycol, shift=-1, axis=0) - ycol                            # OGG:1366-1370
         if numpy.any(dy3_ == 0):

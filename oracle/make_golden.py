@@ -40,6 +40,17 @@ CONFIGS = {  # extras/Makefile:28-39 (file name / subgrid flags dropped; they do
     # BASELINE.json configs[0] geometry through the CLI that exists in this snapshot
     "readme_dp": "-r 2 --lon_dp 60.0 --lat_dp -85.85 --no_changing_meta",
     "res1.0_dp": "-r 1.0 --r_dp 0.2 --south_cutoff_row 2 --no_changing_meta",
+    # BASELINE.json configs[1]: the benchmark's headline workload, no south cut (all 143 kept displaced-pole rows compared)
+    "res0.25_full": "-r 4 --r_dp 0.2 --no_changing_meta",
+    # the reference's own 1/8-degree recipe (extras/Makefile:40-41): match_dy bp + so + p125sc (OGG:1050-1057, 1094-1097, 1123-1125)
+    "res0.125": "-r 8 --r_dp 0.2 --south_cutoff_row 5 --match_dy bp so p125sc --ensure_nj_even --no_changing_meta",
+    # plan branches no extras/Makefile recipe reaches: match_dy bp alone, p125sc alone, the angle cut (OGG:1276-1279),
+    # a row cut that removes the whole southern cap and part of the Southern Ocean band (OGG:1296-1313)
+    "res1.0_bp": "-r 1.0 --r_dp 0.2 --match_dy bp --south_cutoff_row 2 --no_changing_meta",
+    "res1.0_p125sc": "-r 1.0 --r_dp 0.2 --match_dy p125sc --ensure_nj_even --south_cutoff_row 2 --no_changing_meta",
+    "res1.0_cutang": "-r 1.0 --r_dp 0.2 --south_cutoff_ang -80.4 --no_changing_meta",
+    "res1.0_cutso": "-r 1.0 --r_dp 0.2 --south_cutoff_row 45 --no_changing_meta",
+    "res0.5_cutang_regular": "-r 2 --south_cutoff_ang -81.1 --no_changing_meta",
 }
 QUICK = ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp"]
 
@@ -47,6 +58,9 @@ QUICK = ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp"
 def quiet(f, *a, **k):
     with contextlib.redirect_stdout(io.StringIO()):
         return f(*a, **k)
+
+
+LAST_STDOUT = [""]
 
 
 def run_config(R, flags):
@@ -59,7 +73,10 @@ def run_config(R, flags):
     sys.argv = argv
     try:
         g = {"__name__": "__main__", "__file__": H.REFERENCE}
-        quiet(exec, compile(src, H.REFERENCE, "exec"), g)
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            exec(compile(src, H.REFERENCE, "exec"), g)
+        LAST_STDOUT[0] = buf.getvalue()
     finally:
         sys.argv = old
     return netCDF4.LAST["/tmp/golden_tmp.nc"]
@@ -79,6 +96,13 @@ def make_configs(which):
         t0 = time.time()
         v = run_config(R, CONFIGS[name])
         out[name] = {"flags": CONFIGS[name], "arrays": {k: describe(v[k]) for k in ("x", "y", "dx", "dy", "area", "angle_dx")}}
+        # the reference's own stdout for this recipe: the CHECK_metrics self-check lines (OGG:1016, 1069, 1111, 1156, 1172),
+        # the plan messages and its wall time (`runtime(secs)`, OGG:1449; strict numpy loops, one core)
+        lines = LAST_STDOUT[0].splitlines()
+        out[name]["stdout_checks"] = [ln for ln in lines if "CHECK_metrics" in ln]
+        out[name]["stdout_plan"] = [ln for ln in lines if ln.startswith("   Cutting") or "need to be cut" in ln
+                                    or "No SC grid remained" in ln or ln.startswith("   Equator is at") or ln.startswith("shapes:")]
+        out[name]["o1_runtime_secs"] = [float(ln.split()[-1]) for ln in lines if ln.startswith("runtime(secs)")]
         print(name, out[name]["arrays"]["x"]["shape"], "%.1fs" % (time.time() - t0), flush=True)
         json.dump(out, open(path, "w"), indent=1, sort_keys=True)
 

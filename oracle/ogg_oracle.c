@@ -69,24 +69,38 @@ static const double LG[7] = {6.666666666666735130e-01, 3.999999999940941908e-01,
                              1.818357216161805012e-01, 1.531383769920937332e-01,
                              1.479819860511658591e-01};
 
+/* Operation-count hooks: no-ops here.  oracle/opcount.cpp compiles this file with an operator-counting scalar in
+ * place of double and uses them to tell the two kernel polynomials of sincos_parts apart, so that it can also report
+ * the count of an implementation that evaluates only the polynomial a sin / cos call selects (same result bits). */
+#ifndef OGG_OPCOUNT_BEGIN
+#define OGG_OPCOUNT_BEGIN(bucket)
+#define OGG_OPCOUNT_END(bucket)
+#define OGG_OPCOUNT_UNUSED(bucket)
+#endif
 static void sincos_parts(double x, int *n, double *s, double *c) {
   double k = rint(x * TWO_OVER_PI);
   double r = ((x - k * RP1) - k * RP2) - k * RP3;
   double z = r * r;
+  OGG_OPCOUNT_BEGIN(sin_poly)
   double p = SC[1] + z * (SC[2] + z * (SC[3] + z * (SC[4] + z * SC[5])));
   *s = r + (z * r) * (SC[0] + z * p);
+  OGG_OPCOUNT_END(sin_poly)
+  OGG_OPCOUNT_BEGIN(cos_poly)
   double rr = z * (CC[0] + z * (CC[1] + z * (CC[2] + z * (CC[3] + z * (CC[4] + z * CC[5])))));
   double hz = 0.5 * z;
   double w = 1.0 - hz;
   *c = w + (((1.0 - w) - hz) + z * rr);
+  OGG_OPCOUNT_END(cos_poly)
   *n = (int)(((i64)k) & 3);
 }
 static double p_sin(double x) {
   int n; double s, c; sincos_parts(x, &n, &s, &c);
+  if (n & 1) { OGG_OPCOUNT_UNUSED(sin_poly) } else { OGG_OPCOUNT_UNUSED(cos_poly) }
   return n == 0 ? s : (n == 1 ? c : (n == 2 ? -s : -c));
 }
 static double p_cos(double x) {
   int n; double s, c; sincos_parts(x, &n, &s, &c);
+  if (n & 1) { OGG_OPCOUNT_UNUSED(cos_poly) } else { OGG_OPCOUNT_UNUSED(sin_poly) }
   return n == 0 ? c : (n == 1 ? -s : (n == 2 ? -c : s));
 }
 static double p_tan(double x) {

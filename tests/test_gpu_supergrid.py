@@ -27,13 +27,19 @@ def _plan_args(a):
     return {k: v for k, v in a.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta", "write_subgrid_files")}
 
 
+# res0.25_full = the benchmark's headline workload `-r 4 --r_dp 0.2`; res0.125 = the reference's own 1/8-degree recipe
+# (extras/Makefile:40-41: match_dy bp so p125sc); res1.0_bp / _p125sc / _cutang / _cutso, res0.5_cutang_regular = the plan
+# branches no extras/Makefile recipe reaches (OGG:1050-1057, 1123-1125, 1276-1279, 1296-1313)
 @pytest.mark.parametrize("name", ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp", "res0.25",
-                                  "res0.25_om5proto"])
-def test_config_matches_reference_hashes(SG, golden_configs, name):
-    if name not in golden_configs:
-        pytest.skip("no golden entry for %s" % name)
+                                  "res0.25_om5proto", "res0.25_full", "res0.125", "res1.0_bp", "res1.0_p125sc",
+                                  "res1.0_cutang", "res1.0_cutso", "res0.5_cutang_regular"])
+def test_config_matches_reference_hashes(SG, golden_configs, name, capsys):
     cfg = golden_configs[name]
     plan = SG.plan_supergrid(**_plan_args(_args(cfg["flags"])))
+    planned = capsys.readouterr().out
+    for line in cfg.get("stdout_plan", []):        # the reference's own cut messages for this recipe
+        if "Cutting" in line or "need to be cut" in line or "No SC grid remained" in line:
+            assert line in planned.splitlines(), (line, planned)
     got = SG.build_supergrid(plan).to_host()
     for k in NAMES:
         assert list(got[k].shape) == cfg["arrays"][k]["shape"], (k, got[k].shape)

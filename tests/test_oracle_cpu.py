@@ -185,7 +185,10 @@ def test_product_never_imports_oracle():
 
 # ---- whole-supergrid composition of the oracle vs the reference-made per-array hashes -----------------
 @pytest.mark.parametrize("name,kw", [("res4.0", None), ("res1.0", dict(r=1.0, south_cutoff_row=2)),
-                                     ("res1.0_dp", dict(r=1.0, r_dp=0.2, south_cutoff_row=2)), ("res0.5", dict(r=2))])
+                                     ("res1.0_dp", dict(r=1.0, r_dp=0.2, south_cutoff_row=2)), ("res0.5", dict(r=2)),
+                                     ("res1.0_cutso", dict(r=1.0, r_dp=0.2, south_cutoff_row=45)),
+                                     # the benchmark's headline grid (BASELINE.json configs[1]) and bench.py's CPU arm
+                                     ("res0.25_full", dict(r=4, r_dp=0.2))])
 def test_oracle_supergrid_matches_reference_hashes(oracle, golden_configs, name, kw):
     import supergrid_cpu
     from util import sha
@@ -254,3 +257,83 @@ def test_ogg_chksum_known_answer(capsys):
         "fc62429c3e69001d65972cdeb94fb9aa18a7d9c16bc449e1e474e7e41bb95a7d          a min = 0.000000000000000 max = 1.000000000000000 mean = 0.500000000000000 sd = 0.500000000000000\n"
         == out
     )
+
+
+def test_netcdf3_writer_bytes_known_answer(tmp_path):
+    """Spec-derived byte-level known answer for write_nc's container: the file netCDF-C produces for the reference's call
+    sequence (OGG:795-821) on a 2 x 3-cell grid is fixed by the classic-format grammar (magic, numrecs, dim_list, gatt_list,
+    var_list in definition order, each vsize rounded up to 4, 64-bit `begin`s, data contiguous after the header,
+    NC_CHAR padded with NULs, big-endian doubles).  The expected bytes are assembled HERE, independently of netcdf3.py,
+    from that grammar; the first 96 bytes are also written out literally."""
+    import struct
+    import numpy as np
+    from ocean_model_grid_generator_b200 import netcdf3
+    ny, nx = 2, 3
+    nyp, nxp = ny + 1, nx + 1
+    rng = np.random.default_rng(2)
+    shapes = {"y": (nyp, nxp), "x": (nyp, nxp), "dy": (ny, nxp), "dx": (nyp, nx), "area": (ny, nx), "angle_dx": (nyp, nxp)}
+    a = {k: rng.normal(size=s) for k, s in shapes.items()}
+    a["x"][0, 0], a["x"][0, 1] = 1.0, -2.5       # two values whose big-endian images are easy to read in a dump
+
+    be32 = lambda v: struct.pack(">i", v)        # noqa: E731
+    def name(sv):
+        b = sv.encode()
+        return be32(len(b)) + b + b"\0" * (-len(b) % 4)
+    def text_att(k, v):
+        b = v.encode()
+        return name(k) + be32(2) + be32(len(b)) + b + b"\0" * (-len(b) % 4)     # NC_CHAR = 2
+    ABSENT = be32(0) + be32(0)
+    dims = [("nyp", nyp), ("nxp", nxp), ("ny", ny), ("nx", nx), ("string", 255)]
+    var_defs = [("tile", [4], None, 2, 255), ("y", [0, 1], "degrees", 6, 8 * nyp * nxp), ("x", [0, 1], "degrees", 6, 8 * nyp * nxp),
+                ("dy", [2, 1], "meters", 6, 8 * ny * nxp), ("dx", [0, 3], "meters", 6, 8 * nyp * nx),
+                ("area", [2, 3], "m2", 6, 8 * ny * nx), ("angle_dx", [0, 1], "degrees", 6, 8 * nyp * nxp)]
+
+    def expected(gatts):
+        head = b"CDF\x02" + be32(0) + be32(0x0A) + be32(len(dims)) + b"".join(name(n) + be32(v) for n, v in dims)
+        head += (be32(0x0C) + be32(len(gatts)) + b"".join(text_att(k, v) for k, v in gatts)) if gatts else ABSENT
+        head += be32(0x0B) + be32(len(var_defs))
+        entries = []
+        for vname, dimids, units, nctype, nbytes in var_defs:
+            e = name(vname) + be32(len(dimids)) + b"".join(be32(d) for d in dimids)
+            e += (be32(0x0C) + be32(1) + text_att("units", units)) if units else ABSENT
+            entries.append((e + be32(nctype) + be32(nbytes + (-nbytes % 4)), nbytes + (-nbytes % 4)))
+        hlen = len(head) + sum(len(e) + 8 for e, _ in entries)
+        begin, data = hlen, b""
+        for (e, vsize), (vname, _, _, nctype, nbytes) in zip(entries, var_defs):
+            head += e + struct.pack(">q", begin)
+            begin += vsize
+            if nctype == 2:
+                data += b"tile1" + b"\0" * 250 + b"\0"                           # 255 chars + 1 pad byte
+            else:
+                data += a[vname].astype(">f8").tobytes()
+        assert len(head) == hlen
+        return head + data
+
+    out = tmp_path / "k.nc"
+    netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"])
+    raw = out.read_bytes()
+    literal = bytes.fromhex(
+        "43444602" "00000000"                                   # CDF, version 2; numrecs 0
+        "0000000a" "00000005"                                   # NC_DIMENSION, 5 dims
+        "00000003" "6e797000" "00000003"                        # nyp = 3
+        "00000003" "6e787000" "00000004"                        # nxp = 4
+        "00000002" "6e790000" "00000002"                        # ny = 2
+        "00000002" "6e780000" "00000003"                        # nx = 3
+        "00000006" "737472696e670000" "000000ff"                # string = 255
+        "00000000" "00000000"                                   # no global attributes
+        "0000000b" "00000007")                                  # NC_VARIABLE, 7 variables
+    assert raw[:len(literal)] == literal
+    assert raw == expected(None)
+    # first variable entry, literally: "tile", 1 dim (id 4), no attributes, NC_CHAR, vsize 256, begin = header length
+    tile = bytes.fromhex("00000004" "74696c65" "00000001" "00000004" "00000000" "00000000" "00000002" "00000100")
+    assert raw[len(literal):len(literal) + len(tile)] == tile
+    hlen = struct.unpack(">q", raw[len(literal) + len(tile):len(literal) + len(tile) + 8])[0]
+    assert raw[hlen:hlen + 5] == b"tile1" and raw[hlen + 5:hlen + 256] == b"\0" * 251
+    # x[0,0] = 1.0 and x[0,1] = -2.5 as big-endian IEEE doubles at x's begin (= header + tile + y)
+    xbeg = hlen + 256 + 8 * nyp * nxp
+    assert raw[xbeg:xbeg + 16] == bytes.fromhex("3ff0000000000000" "c004000000000000")
+    # with the three global attributes of a normal run (OGG:822-826), in the reference's order
+    gatts = [("history", "made by a test"), ("description", "2 x 3 cells."), ("source", "src")]
+    netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], global_attrs=gatts)
+    assert out.read_bytes() == expected(gatts)
+    assert len(out.read_bytes()) % 4 == 0
