@@ -8,6 +8,10 @@ One step = one build of the whole workload supergrid (every rank builds its lati
 sub-grid, then the global-area check: device reduction + one all-reduce when N > 1).
 N=1 workload: BASELINE.json configs[1], `-r 4 --r_dp 0.2` (2243 x 2881 vertices).  For N > 1 the resolution grows
 with N so that the vertices per GPU stay ~6.5-7.3e6 (weak scaling): N=2: r=6, N=4: r=8, N=8: r=12.
+The same line also carries, outside the timed region of the metric: `strong` -- BASELINE configs[2..4] (1/8, 1/30, 1/120
+degree) as fixed-size runs in 8 row-slabs on the N GPUs of this launch (area and device checksums must not depend on N);
+`halo_midas` (N > 1) -- the supplied-mesh MIDAS entry point with its one-row halo over NCCL send/recv, checked bit for
+bit; `cli` (N = 1) -- wall time of the real entry point main() -> write_nc.
 Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for the roofline arithmetic.
 """
 import argparse
@@ -24,19 +28,40 @@ sys.path.insert(0, ROOT)
 METRIC = "supergrid points/s (coords+metrics, FP64)"
 UNIT = "points/s"
 WEAK_RESOLUTION = {1: 4, 2: 6, 4: 8, 8: 12}
-
-# ---- algorithmic FP64 work per unit (DESIGN.md "Work per unit"): +,-,* count 1; / counts W_DIV and sqrt W_SQRT,
-# the FP64-pipe instructions of the IEEE-correct expansions on sm_100a (fast paths seen in SASS)
-W_DIV, W_SQRT = 10, 9
-OPS_BP_SAMPLE = 165 + 7 * W_DIV + 3 * W_SQRT                 # bipolar metrics-only sample (k_bp_lattice<1>)
-OPS_DP_VERTEX = 87 + 5 * W_DIV + 1 * W_SQRT
-OPS_HAVERSINE = 192 + 1 * W_DIV + 1 * W_SQRT
-OPS_DP_SAMPLE = 8 * OPS_DP_VERTEX + 4 * OPS_HAVERSINE + 8 + 24   # order-4 differences, 8 projections (k_dp_hsamples<2>)
 BYTES_BAND_VERTEX = 48
-# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the default workload's kernels, from the committed
-# `ncu --set full` capture profiles/r01e_ncu_full_summary.csv -- not measured in this run; valid for `-r 4 --r_dp 0.2` only.
-# The cap kernels are FP64-bound and move almost nothing (O(Ni+Nj) tables in, samples parked in the 126 MB L2).
-NCU_TRAFFIC_R4 = {"dp_hsamples": 774144 + 6492672, "bipolar_quad_fused": 352256 + 24576, "band_fill": 326400 + 140988672}
+# BASELINE.json configs[2..4] as fixed-size (strong-scaling) runs: (flags, row-slabs V, timed steps).  V = 8 on every N so
+# that the 1/120-degree grid (279 GB) fits one GPU slab by slab and the same slabs are built on 1, 2, 4 and 8 GPUs.
+STRONG_CONFIGS = [("r8", "-r 8 --r_dp 0.2", 8, 10), ("r30", "-r 30 --r_dp 0.2 --ensure_nj_even", 8, 5),
+                  ("r120", "-r 120 --r_dp 0.2", 8, 3)]
+
+
+def load_opcount():
+    """Per-unit FP64 operation counts DERIVED from the oracle by tools/opcount.py (profiles/opcount.json, committed; a CPU
+    test re-derives them).  ops_8d: SURVEY 8(d) weights (every + - * / sqrt compare = 1) on what an implementation must
+    execute for the same bits; ops_issue: FP64-pipe instructions of the IEEE expansions (division 8, cached divisor 3,
+    square root 8); ops_reference: 8(d) weights on everything the reference evaluates per unique sample (orientation)."""
+    d = json.load(open(os.path.join(ROOT, "profiles", "opcount.json")))
+    t = d["totals"]
+    return {"dp_hsamples": t["dp_hsample"], "bipolar_quad_fused": t["bipolar_sample"]}
+
+
+def load_ncu_summary():
+    """Hardware counters of the committed `ncu --set full` capture (profiles/ncu_summary.json, written by
+    tools/profile_summaries.py): per kernel the DRAM bytes per launch and the FP64-pipe busy fraction, with the commit the
+    capture was taken at.  Not measured in this run -- reported beside the live numbers and labelled as such."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
+    except Exception:
+        return {}
+
+
+def config_of(wl, nyp, nxp, world, slabs, per_rank):
+    """The `config` object: identical for the GPU arm and the CPU reference arm of the same launch."""
+    sharding = ("latitude row-slabs of every sub-grid, %d rank(s); weak scaling: r=4/6/8/12 at N=1/2/4/8" % world) if not slabs else (
+        "%d latitude row-slabs of every sub-grid, %d per rank, built one after the other in one slab's buffers "
+        "(strong scaling: the grid is fixed)" % (slabs, per_rank))
+    return {"workload": "%s: full tripolar supergrid %dx%d vertices (displaced-pole cap + Southern Ocean + Mercator + "
+                        "bipolar cap), x,y,dx,dy,area,angle_dx" % (wl, nyp, nxp), "sharding": sharding}
 
 
 def parse():
@@ -52,6 +77,8 @@ def parse():
                         "slabs g, g+N, ... one after the other in one slab's worth of buffers (V %% N == 0)")
     p.add_argument("--no_cpu_baseline", action="store_true")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--no_strong", action="store_true", help="skip the fixed-size runs of BASELINE configs[2..4] (1/8, 1/30, 1/120 degree)")
+    p.add_argument("--no_cli", action="store_true", help="skip the timing of the CLI entry point (main -> write_nc)")
     return p.parse_args()
 
 
@@ -136,11 +163,33 @@ def use_all_host_threads():
     os.environ["OMP_NUM_THREADS"] = str(n)
 
 
-def cpu_pass(r, r_dp):
+def grid_shape_cpu(r, r_dp):
+    """(nyp, nxp) of `-r R --r_dp X` from the sizing rules alone (OGG:969-1195, default flags): no array is built."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import ogg_oracle
+    Ni = int(r * 2 * 360)
+    phi_s, phi_n = (-68.0, 65.0) if r == 2 else (-66.85954725, 64.05895973)
+    nM = ogg_oracle.mercator_phi_1d(Ni, phi_s, phi_n, True, False).shape[0]
+    nBP = (119 * 2 if r == 2 else int(60 * r * 2)) + 1
+    nSO = int(r * 55) + 1
+    Nj_scap = int(r * 40) * 7 // 4
+    if r_dp == 0.0:
+        nSC = int((-78.0 + 90.0) / (1.0 / r / 2)) + 1
+    else:
+        jmin = np.ceil(0.49 * Nj_scap)
+        nSC = Nj_scap + 1 - int(jmin + np.mod(jmin, 2))
+    return (nSC - 1) + (nSO - 1) + (nM - 1) + nBP, Ni + 1
+
+
+def cpu_pass(r, r_dp, world=1):
+    """One timed pass of the CPU arm.  world == 1: the whole grid.  world > 1: rank 0's row-slab share of every sub-grid
+    (1/world of the rows of each -- the work one GPU does per step), a bounded representative sample of the larger grid;
+    points/s = vertices evaluated / time either way."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import supergrid_cpu
     t0 = time.time()
-    out = supergrid_cpu.build_cpu(r, r_dp=r_dp)
+    out = supergrid_cpu.build_cpu(r, r_dp=r_dp, slab=(0, world) if world > 1 else None)
     dt = time.time() - t0
     return out["x"].size / dt, dt, out["x"].shape
 
@@ -149,39 +198,51 @@ def cpu_baseline(r, r_dp):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ogg_oracle
     cores = ogg_oracle.num_threads()
-    rr = r if r <= 4 else 4   # bounded sample: the 1/4-degree grid costs ~10-30 s of CPU work
-    pps, dt, shape = cpu_pass(rr, r_dp)
-    return {"value": pps, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "one pass of '-r %s --r_dp %s' (%dx%d vertices, whole grid, %.1f s) through oracle/ (C restatement "
-                      "of the reference, OpenMP)" % (rr, r_dp, shape[0], shape[1], dt)}
+    pps, dt, shape = cpu_pass(r, r_dp)
+    o1 = {}
+    try:
+        g = json.load(open(os.path.join(ROOT, "tests", "golden", "configs.json")))["res0.25_full"]
+        o1 = {"o1_unmodified_reference_runtime_secs": g["o1_runtime_secs"][0],
+              "o1_note": "the unmodified Python reference (numpy + this repo's portable-trig twin, strict loops, 1 core) for "
+                         "'-r 4 --r_dp 0.2', its own runtime(secs) line (OGG:1449), measured in the build container by "
+                         "oracle/make_golden.py; the reference itself cannot travel to the GPU box"}
+    except Exception:
+        pass
+    return dict({"value": pps, "unit": UNIT, "cores": cores, "kind": "port",
+                 "sample": "one pass of '-r %s --r_dp %s' (%dx%d vertices, whole grid, %.1f s) through oracle/ (C restatement "
+                           "of the reference, OpenMP)" % (r, r_dp, shape[0], shape[1], dt)}, **o1)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     r, wl = workload(args)
-    rr = r if r <= 4 else 4
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     use_all_host_threads()
     import ogg_oracle
     cores = ogg_oracle.num_threads()
-    for _ in range(min(args.warmup, 1)):
-        cpu_pass(rr, args.r_dp)
-    steps = max(1, min(args.steps, 5))
+    nyp, nxp = grid_shape_cpu(r, args.r_dp)
+    for _ in range(args.warmup):
+        cpu_pass(r, args.r_dp, world)
     t0 = time.time()
-    shape = None
-    for _ in range(steps):
-        _, _, shape = cpu_pass(rr, args.r_dp)
-    dt = (time.time() - t0) / steps
-    pps = shape[0] * shape[1] / dt
-    line = {"impl": "reference", "metric": METRIC, "value": pps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-            "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+    pts = 0
+    for _ in range(args.steps):
+        _, _, shape = cpu_pass(r, args.r_dp, world)
+        pts += shape[0] * shape[1]
+    dt = (time.time() - t0) / args.steps
+    pps = pts / (dt * args.steps)
+    sample = ("whole '%s' grid per step" % wl) if world == 1 else (
+        "per step: rank 0's row-slab share (1/%d of every sub-grid's rows, %dx%d vertices -- what one of the %d GPUs builds "
+        "per step) of '%s'" % (world, shape[0], shape[1], world, wl))
+    line = {"impl": "reference", "metric": METRIC, "value": pps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "-r %s --r_dp %s (%dx%d vertices); CPU arm bounded to r<=4" % (rr, args.r_dp, shape[0], shape[1])},
+            "config": config_of(wl, nyp, nxp, world, 0, 1),
             "cpu_baseline": {"value": pps, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": "whole '-r %s --r_dp %s' grid per step, oracle/ C restatement with OpenMP; the reference "
-                                       "itself is pure Python + the absent numpypi and cannot travel to this box" % (rr, args.r_dp)},
+                             "sample": sample + "; oracle/ C restatement of the reference with OpenMP on all host threads (the "
+                                       "reference itself is pure Python + the absent numpypi and cannot travel to this box)"},
             "e2e": {"value": pps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line))
 
@@ -189,6 +250,138 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------------
+def _plan_for(flags):
+    import contextlib
+    import io
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G, supergrid as SG
+    a = vars(G._build_parser().parse_args(flags.split()))
+    plan_args = {k: v for k, v in a.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta", "write_subgrid_files")}
+    with contextlib.redirect_stdout(io.StringIO()):
+        return SG.plan_supergrid(**plan_args), plan_args
+
+
+def _u64(t):
+    return ["%016x" % (int(v) & 0xffffffffffffffff) for v in t.cpu().tolist()]
+
+
+def run_fixed_grid(flags, V, steps, rank, world, dist, whole_check=False):
+    """Strong scaling on a fixed grid cut into V row-slabs (V % world == 0): rank g builds slabs g, g+N, ... one after the
+    other in one slab's buffers, then the single global-area all-reduce.  Returns ms per build of the whole grid (device
+    time, max over ranks), the all-reduced area and the per-array device checksums summed over all slabs (additive, so
+    they must not depend on N)."""
+    import torch
+    from ocean_model_grid_generator_b200 import _cabi, device as D, supergrid as SG
+    plan, _ = _plan_for(flags)
+    mine = list(range(rank, V, world))
+    sg = SG.Supergrid(plan, mine[0], V, capacity_world=V)
+    area_parts = torch.zeros(len(mine), dtype=torch.float64, device="cuda")
+    acc = torch.zeros(6, dtype=torch.int64, device="cuda")
+
+    def step(checks=False):
+        for n, v in enumerate(mine):
+            sg.set_slab(v, V).build()
+            _cabi.call("ogg_sum_strided", D.ptr(sg.area), sg.area.numel(), 1, D.ptr_off(area_parts, n), D.stream())
+            if checks:
+                sg.checksums(acc)
+        if dist is not None:
+            dist.all_reduce(area_parts)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step(checks=True)                       # warm-up pass; also the checksum pass (not timed)
+    area_mine = area_parts.clone()          # after the all-reduce: every rank's per-position sums
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(acc)                # int64 sums wrap mod 2**64, which is the checksum's arithmetic
+    ms = float(t[0]) / steps
+    npoints = plan.nyp * plan.nxp
+    out = {"workload": flags, "grid": [plan.nyp, plan.nxp], "slabs": V, "steps": steps, "ms_per_step": ms,
+           "value": npoints / (ms * 1e-3), "unit": UNIT, "area_m2": float(area_mine.sum()),
+           "checksums_x_y_dx_dy_area_angle": _u64(acc)}
+    del sg
+    if whole_check and rank == 0:
+        whole = SG.Supergrid(plan).build()
+        out["checksums_equal_whole_grid"] = _u64(whole.checksums()) == out["checksums_x_y_dx_dy_area_angle"]
+        del whole
+    torch.cuda.empty_cache()
+    return out
+
+
+def halo_midas_check(plan, rank, world, dist):
+    """The general supplied-mesh entry point on a slab-distributed mesh: generate_grid_metrics_MIDAS (OGG:687-716) with the
+    one-row halo received from the next rank over NCCL send/recv (slabs.metrics_midas_slab).  Mesh = this workload's bipolar
+    cap (non-separable).  Every rank compares its dx, dy, area bit for bit with the rows of the whole-mesh result."""
+    import contextlib
+    import io
+    import torch
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G, slabs
+    p = [pc for pc in plan.pieces if pc.kind == "bipolar"][0].p
+    with contextlib.redirect_stdout(io.StringIO()):
+        xw, yw, _, _ = G.generate_bipolar_cap_mesh(plan.Ni, p["Nj"], p["lat0_bp"], p["lon_bp"], ensure_nj_even=False, device=True)
+    nyp = xw.shape[0]
+    v0, v1 = slabs.vertex_rows(nyp - 1, rank, world)
+    c0, c1 = slabs.slab_bounds(nyp - 1, rank, world)
+    xs, ys = xw[v0:v1].contiguous(), yw[v0:v1].contiguous()
+    got = slabs.metrics_midas_slab(xs, ys)
+    ref = G.generate_grid_metrics_MIDAS(xw, yw)
+    ok = all(g.shape == r_.shape and bool((g.view(torch.int64) == r_.view(torch.int64)).all())
+             for g, r_ in zip(got, (ref[0][v0:v1], ref[1][c0:c1], ref[2][c0:c1])))
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        slabs.metrics_midas_slab(xs, ys)
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / reps, 0.0 if ok else 1.0], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"mesh": "bipolar cap %dx%d vertices in %d row-slabs" % (nyp, xw.shape[1], world), "ms": float(t[0]),
+            "halo_bytes_per_boundary": 16 * int(xw.shape[1]), "transport": "NCCL send/recv (torch.distributed batch_isend_irecv)",
+            "bit_equal_to_whole": float(t[1]) == 0.0}
+
+
+def cli_timing(wl):
+    """The reference's real entry point, end to end: main() -> plan -> build -> CHECK_metrics lines -> write_nc (OGG:855-1449),
+    wall time from its own `runtime(secs)` line (OGG:1449); the file goes to a temporary directory."""
+    import contextlib
+    import io
+    import shutil
+    import tempfile
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    tmp = tempfile.mkdtemp(prefix="ogg_cli_")
+    path = os.path.join(tmp, "ocean_hgrid.nc")
+    runs, size = [], 0
+    try:
+        for _ in range(3):
+            buf = io.StringIO()
+            with contextlib.redirect_stdout(buf):
+                G.cli(["-f", path] + wl.split())
+            runs += [float(ln.split()[-1]) for ln in buf.getvalue().splitlines() if ln.startswith("runtime(secs)")]
+            size = os.path.getsize(path)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    o1 = None
+    try:
+        o1 = json.load(open(os.path.join(ROOT, "tests", "golden", "configs.json")))["res0.25_full"]["o1_runtime_secs"][0]
+    except Exception:
+        pass
+    return {"command": "ocean_grid_generator.py -f ocean_hgrid.nc " + wl, "runtime_secs": sorted(runs)[len(runs) // 2], "runs": runs,
+            "file_bytes": size, "o1_unmodified_reference_runtime_secs_build_container": o1 if wl.strip() == "-r 4 --r_dp 0.2" else None}
+
+
 def run_ours(args):
     import ctypes
     import torch
@@ -201,17 +394,12 @@ def run_ours(args):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from ocean_model_grid_generator_b200 import _cabi, device as D, supergrid as SG
-    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
     D.ready()
     lib = _cabi.load()
     r, wl = workload(args)
-    flags = vars(G._build_parser().parse_args(wl.split()))
-    plan_args = {k: v for k, v in flags.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta",
-                                                              "write_subgrid_files")}
     import contextlib
     import io
-    with contextlib.redirect_stdout(io.StringIO()):
-        plan = SG.plan_supergrid(**plan_args)
+    plan, plan_args = _plan_for(wl)
     V = args.slabs if args.slabs else world
     if V % world:
         raise SystemExit("--slabs must be a multiple of --gpus")
@@ -245,7 +433,7 @@ def run_ours(args):
     # ---- timed region: K steps, CUDA events on the launching stream, per-kernel events inside --------------
     sampler = ClockSampler(local)
     lib.ogg_timing_reset()
-    lib.ogg_timing_enable(2)     # event brackets around the three heavy kernel classes only (4 launches of 21 per step)
+    lib.ogg_timing_enable(2)     # event brackets around the three heavy kernel classes only
     l0 = lib.ogg_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.start()
@@ -293,8 +481,8 @@ def run_ours(args):
     if not args.no_e2e and not args.slabs:
         pinned = None
         area_e2e = D.empty(1)
-        times = []
-        for it in range(4):
+        times, plans = [], []
+        for it in range(6):
             torch.cuda.synchronize()
             if dist is not None:
                 dist.barrier()
@@ -302,6 +490,7 @@ def run_ours(args):
             with contextlib.redirect_stdout(io.StringIO()):
                 p2 = SG.plan_supergrid(**plan_args)
                 s2 = SG.Supergrid(p2, rank, world)
+            t1 = time.perf_counter()
             if pinned is None:
                 pinned = s2.pinned_like()
             s2.build(host=pinned)        # every piece's rows are copied out on its own stream while the caps compute
@@ -315,13 +504,31 @@ def run_ours(args):
             if dist is not None:
                 dist.barrier()
             times.append(time.perf_counter() - t0)
-        te = torch.tensor([min(times[1:])], dtype=torch.float64, device="cuda")
+            plans.append(t1 - t0)
+        timed = sorted(times[1:])                         # the first iteration allocates the pinned buffers
+        te = torch.tensor([timed[len(timed) // 2], sorted(plans[1:])[len(plans[1:]) // 2]], dtype=torch.float64, device="cuda")
         if dist is not None:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         d2h = sum(v.numel() * 8 for v in pinned.values()) + 8
         h2d = sum(8 * (len(pc.p["lam"]) + len(pc.p["phi"])) for pc in plan.pieces if pc.kind == "band") + 8 * (plan.Ni + 1) + 4096
         e2e = {"value": npoints / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "ms": float(te[0]) * 1e3, "checksum_area_local": checksum, "host_area_last_cell": corner}
+               "ms": float(te[0]) * 1e3, "statistic": "median of 5 timed iterations (max over ranks), after one untimed",
+               "plan_ms": float(te[1]) * 1e3, "d2h_gbs_this_rank": d2h / max(1e-9, float(te[0]) - float(te[1])) / 1e9,
+               "checksum_area_local": checksum, "host_area_last_cell": corner}
+        del pinned
+
+    # ---- N > 1: the halo path on the wire; every N: the fixed-size (strong-scaling) runs of configs[2..4] -------------
+    halo = halo_midas_check(plan, rank, world, dist) if dist is not None else None
+    strong = None
+    if not args.no_strong and not args.slabs and args.resolution <= 0:
+        del sg
+        torch.cuda.empty_cache()
+        strong = {}
+        for tag, flags, Vs, nsteps in STRONG_CONFIGS:
+            strong[tag] = run_fixed_grid(flags, Vs, nsteps, rank, world, dist, whole_check=(tag == "r8"))
+    cli = None
+    if rank == 0 and world == 1 and not args.no_cli and not args.slabs:
+        cli = cli_timing(wl)
 
     if rank != 0:
         if dist is not None:
@@ -354,62 +561,71 @@ def run_ours(args):
     # SMs, so a bracket around one of them also spans the other's CTAs; what the timed region does give cleanly is the
     # span during which at least one of the pair was in flight (ogg_timing_pair_span) -- `achieved` = the algorithmic
     # ops of both / that span.  Each kernel alone (single-stream pass) is reported beside it.
-    roof = None
+    ops = load_opcount()
+    ncu = load_ncu_summary()
     kernels_ms = {k: round(v[0] / args.steps, 4) for k, v in sorted(kern_all.items(), key=lambda kv: -kv[1][0])}
-    quad_ops = OPS_DP_SAMPLE * units.get("dp_hsamples", 0) + OPS_BP_SAMPLE * units.get("bipolar_quad_fused", 0)
+    names = [n for n in ("dp_hsamples", "bipolar_quad_fused") if n in units]
 
-    def alone(name, ops):
-        if name not in kern_all or name not in units:
-            return None
-        per = kern_all[name][0] / args.steps
-        ach = ops * units[name] / (per * 1e-3) / 1e12
-        return {"kernel": name, "bound": "fp64", "achieved": ach, "peak": fp64_peak_tf, "unit": "TFLOP/s", "frac": ach / fp64_peak_tf,
-                "ops_per_unit": ops, "units_per_step": units[name], "kernel_ms_per_step": per,
-                "measured_in": "single-stream pass: the kernel has the GPU to itself"}
-    roof_dp, roof_bp = alone("dp_hsamples", OPS_DP_SAMPLE), alone("bipolar_quad_fused", OPS_BP_SAMPLE)
-    if quad_ops and span_n.value:
-        per_step_ms = span_ms.value / args.steps
-        ach = quad_ops / (per_step_ms * 1e-3) / 1e12
-        names = [n for n in ("dp_hsamples", "bipolar_quad_fused") if n in units]
-        roof = {"kernel": " + ".join(names), "bound": "fp64", "achieved": ach, "peak": fp64_peak_tf, "unit": "TFLOP/s",
-                "frac": ach / fp64_peak_tf,
-                "traffic": sum(NCU_TRAFFIC_R4[n] for n in names) if (r == 4 and world == 1 and not args.slabs) else None,
-                "traffic_source": "profiles/r01e_ncu_full_summary.csv (ncu --set full, bytes per launch, both kernels)",
-                "ops_per_step": quad_ops, "ops_per_unit": {"dp_hsamples": OPS_DP_SAMPLE, "bipolar_quad_fused": OPS_BP_SAMPLE},
-                "units_per_step": {n: units[n] for n in names}, "kernel_ms_per_step": per_step_ms,
-                "share_of_step": per_step_ms / (ms / args.steps),
-                "measured_in": "timed region: the two cap quadratures co-run on two streams; span during which at least one "
-                               "of them is in flight (CUDA events on their streams)",
+    def rates(per_ms, which):
+        tot = {w: sum(ops[n][w] * units[n] for n in which) for w in ("ops_8d", "ops_issue", "ops_reference")}
+        return {w: tot[w] / (per_ms * 1e-3) / 1e12 for w in tot}, tot
+
+    def roof_of(which, per_ms, where):
+        rt, tot = rates(per_ms, which)
+        hw = {n: ncu.get("kernels", {}).get(n) for n in which}
+        traffic = None
+        if all(hw.get(n) for n in which) and r == 4 and world == 1 and not args.slabs:
+            traffic = sum(hw[n]["dram_bytes_per_launch"] for n in which)
+        return {"kernel": " + ".join(which), "bound": "fp64", "unit": "TFLOP/s", "peak": fp64_peak_tf,
+                "achieved": rt["ops_8d"], "frac": rt["ops_8d"] / fp64_peak_tf,
+                "achieved_issue": rt["ops_issue"], "frac_issue": rt["ops_issue"] / fp64_peak_tf,
+                "frac_reference_ops": rt["ops_reference"] / fp64_peak_tf,
+                "pipe_fp64_busy_ncu": {n: (hw[n] or {}).get("pipe_fp64_pct") for n in which},
+                "ncu_capture": ncu.get("capture"),
+                "traffic": traffic,
+                "ops_per_unit": {n: {w: round(ops[n][w], 2) for w in ("ops_8d", "ops_issue", "ops_reference")} for n in which},
+                "units_per_step": {n: units[n] for n in which}, "ops_per_step": {w: tot[w] for w in tot},
+                "kernel_ms_per_step": per_ms, "measured_in": where,
+                "definitions": "frac: SURVEY 8(d) weights (+ - * / sqrt compare = 1 op) on the minimal per-unit count derived from "
+                               "the oracle (profiles/opcount.json); frac_issue: the same count weighted by the FP64-pipe instructions "
+                               "of the IEEE expansions (div 8, cached divisor 3, sqrt 8); frac_reference_ops: 8(d) weights on what the "
+                               "reference evaluates per unique sample (un-hoisted, both trig polynomials) -- above 1 means the kernel "
+                               "does less arithmetic than the reference for the same bits, not that it beats the pipe; "
+                               "pipe_fp64_busy_ncu: sm__inst_executed_pipe_fp64 of the committed capture (not this run)",
                 "peak_source": "measured in this run: DADD+DMUL issue rate with FMA contraction off (ogg_fp64_issue_rate); "
                                "MEASURED_PEAKS.json has no FP64 entry"}
-    elif "band_fill" in kern and "band_fill" in units:
-        per_step_ms = kern["band_fill"][0] / args.steps
-        ach = BYTES_BAND_VERTEX * units["band_fill"] / (per_step_ms * 1e-3) / 1e9
-        roof = {"kernel": "band_fill", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                "traffic": None, "peak_source": hbm_src, "kernel_ms_per_step": per_step_ms,
-                "share_of_step": per_step_ms / (ms / args.steps)}
+    roof = roof_dp = roof_bp = None
+    if names and span_n.value:
+        per_step_ms = span_ms.value / args.steps
+        roof = roof_of(names, per_step_ms, "timed region: the two cap quadratures co-run on two streams; span during which at least "
+                                           "one of them is in flight (CUDA events on their streams)")
+        roof["share_of_step"] = per_step_ms / (ms / args.steps)
+    alone = "single-stream pass: the kernel has the GPU to itself"
+    if "dp_hsamples" in units and "dp_hsamples" in kern_all:
+        roof_dp = roof_of(["dp_hsamples"], kern_all["dp_hsamples"][0] / args.steps, alone)
+    if "bipolar_quad_fused" in units and "bipolar_quad_fused" in kern_all:
+        roof_bp = roof_of(["bipolar_quad_fused"], kern_all["bipolar_quad_fused"][0] / args.steps, alone)
     roof_hbm = None
     if "band_fill" in kern_all and "band_fill" in units:
         per_step_ms = kern_all["band_fill"][0] / args.steps
         ach = BYTES_BAND_VERTEX * units["band_fill"] / (per_step_ms * 1e-3) / 1e9
         roof_hbm = {"kernel": "band_fill", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                     "frac": ach / hbm_peak, "peak_source": hbm_src, "kernel_ms_per_step": per_step_ms,
+                    "traffic": (ncu.get("kernels", {}).get("band_fill") or {}).get("dram_bytes_per_launch_all_band_launches"),
                     "measured_in": "single-stream pass (in the timed region the band fills overlap the cap kernels)"}
+    if roof is None:
+        roof = roof_hbm
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.slabs else "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": "%s: full tripolar supergrid %dx%d vertices (displaced-pole cap + Southern Ocean + Mercator + "
-                                   "bipolar cap), x,y,dx,dy,area,angle_dx" % (wl, plan.nyp, plan.nxp),
-                       "sharding": ("latitude row-slabs of every sub-grid, %d rank(s); weak scaling: r=4/6/8/12 at N=1/2/4/8" % world)
-                       if not args.slabs else ("%d latitude row-slabs of every sub-grid, %d per rank, built one after the other in "
-                                               "one slab's buffers (strong scaling: the grid is fixed)" % (V, len(mine))),
-                       "cache": "each step rewrites %.0f MB of outputs + scratch, larger than the 126 MB L2; no flush needed"
-                                % (npoints * 48 / 1e6),
-                       "global_area_m2": total_area},
+            "config": config_of(wl, plan.nyp, plan.nxp, world, args.slabs, len(mine)),
+            "cache": "each step rewrites %.0f MB of outputs + scratch, larger than the 126 MB L2; no flush needed" % (npoints * 48 / 1e6),
+            "global_area_m2": total_area,
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "roofline_dp_hsamples": roof_dp, "roofline_bipolar_quad": roof_bp, "roofline_band_hbm": roof_hbm,
             "kernels_ms_per_step_single_stream_pass": kernels_ms,
-            "kernels_ms_per_step_timed_region": {k: round(v[0] / args.steps, 4) for k, v in kern.items()}, "fp64_issue_peak_tflops_measured": fp64_peak_tf}
+            "kernels_ms_per_step_timed_region": {k: round(v[0] / args.steps, 4) for k, v in kern.items()}, "fp64_issue_peak_tflops_measured": fp64_peak_tf,
+            "halo_midas": halo, "strong": strong, "cli": cli}
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(r, args.r_dp)
     elif world > 1:

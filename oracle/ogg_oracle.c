@@ -420,6 +420,13 @@ static void quad_cells(int order, i64 nx, i64 ny, const double *dx, const double
   }
 }
 
+/* exported face of quad_cells for row-slab compositions (oracle/supergrid_cpu.py): dx, dy are the [order*(ny+1)][order*(nx+1)]
+ * sample arrays of ANY ny consecutive cell rows (+ the ghost row), exactly as OGG:174-187 / :585-599 consume them */
+void ogo_quad_cells(int order, i64 nx, i64 ny, const double *dx, const double *dy, double Re, double *dxq, double *dyq,
+                    double *daq) {
+  quad_cells(order, nx, ny, dx, dy, Re, dxq, dyq, daq);
+}
+
 /* OGG:136-188. returns 0, or -1 for an uncoded order */
 int ogo_bipolar_cap_metrics_quad_fast(int order, i64 nx, i64 ny, double lat0_bp, double lon_bp, double rp,
                                       double Re, double *dxq, double *dyq, double *daq) {

@@ -121,6 +121,26 @@ def bipolar_cap_metrics_quad_fast(order, nx, ny, lat0_bp, lon_bp, rp, Re=_defaul
     return dxq, dyq, daq
 
 
+def sample_index(order, c0, c1, total, fudge=False):
+    """j1d / i1d of OGG:143-156, 573-581 for cells [c0, c1] (c1 = the ghost cell that closes the slab): order nodes per
+    cell; with `fudge`, a node equal to `total` becomes total - 0.001 (OGG:146-147)."""
+    a, b = quad_positions(order)
+    c = np.arange(c0, c1 + 1, dtype=np.float64)
+    v = (b[None, :] * c[:, None] + a[None, :] * (c[:, None] + 1)).reshape(-1)
+    if fudge:
+        last = v.reshape(-1, order)[:, order - 1]
+        last[last == float(total)] = float(total) - 0.001
+    return np.ascontiguousarray(v)
+
+
+def quad_cells(order, nx, ny, dx, dy, Re=_default_Re):
+    """Tail of OGG:174-187 / 585-599 on sample arrays [order*(ny+1)][order*(nx+1)] -> dxq [ny+1][nx], dyq [ny][nx+1], daq [ny][nx]."""
+    dx, dy = _c(dx), _c(dy)
+    dxq, dyq, daq = np.empty((ny + 1, nx)), np.empty((ny, nx + 1)), np.empty((ny, nx))
+    lib().ogo_quad_cells(_int(order), _i64(nx), _i64(ny), _p(dx), _p(dy), _d(Re), _p(dxq), _p(dyq), _p(daq))
+    return dxq, dyq, daq
+
+
 def quad_positions(n=3):
     a, b = np.empty(5), np.empty(5)
     if lib().ogo_quad_positions(_int(n), _p(a), _p(b)):

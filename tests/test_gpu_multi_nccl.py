@@ -127,7 +127,7 @@ def _gather_ragged(dist, bufs, t, rank, world):
 @pytest.mark.parametrize("flags", ["-r 1.0 --r_dp 0.2", "-r 2"])
 def test_nccl_slabs_halo_allreduce(flags):
     import torch.multiprocessing as mp
-    world = min(_ngpu(), 4)
+    world = min(_ngpu(), 8)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -139,3 +139,41 @@ def test_nccl_slabs_halo_allreduce(flags):
         p.join(timeout=60)
     bad = [(r, w) for r, ok, w in got if not ok]
     assert not bad, bad
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_one_process_drives_two_devices():
+    """SURVEY 8(b) allows one process driving several devices: the library's per-device state (SM count, the opt-in to
+    53 KB of dynamic shared memory of the fused bipolar kernel, the scratch pool, timing events) must follow
+    cudaSetDevice.  The same calls on device 1 after device 0 give the same bits, and the timing brackets of each device
+    are reported on that device."""
+    import ctypes
+    import torch
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from ocean_model_grid_generator_b200 import _cabi, device as D, ocean_grid_generator as G, supergrid as SG
+    D.ready()
+    lib = _cabi.load()
+    lib.ogg_timing_reset()
+    lib.ogg_timing_enable(1)
+    results = []
+    for dev in (0, 1, 0):
+        with torch.cuda.device(dev):
+            rp = G.bipolar_rp(64.05895973)
+            bp = G.bipolar_cap_metrics_quad_fast(5, 96, 16, 64.05895973, -300.0, rp)
+            dp = G.displacedPoleCap_metrics_quad(4, 48, 10, -300.0, -78.0, 80.0, 0.2)
+            a = vars(G._build_parser().parse_args("-r 0.5 --r_dp 0.2".split()))
+            pa = {k: v for k, v in a.items() if k not in ("gridfilename", "debug", "plotem", "no_changing_meta", "write_subgrid_files")}
+            sg = SG.build_supergrid(SG.plan_supergrid(**pa)).to_host()
+            torch.cuda.synchronize()
+            tot, n = ctypes.c_double(), ctypes.c_longlong()
+            kid = {lib.ogg_timing_name(k).decode(): k for k in range(lib.ogg_timing_kernels())}
+            assert lib.ogg_timing_get(kid["bipolar_quad_fused"], ctypes.byref(tot), ctypes.byref(n)) == 0
+            assert n.value >= 2 and tot.value > 0        # this device's brackets only; elapsed times are valid
+            results.append([np.asarray(v) for v in bp + dp] + [sg[k] for k in ("x", "y", "dx", "dy", "area", "angle_dx")])
+    lib.ogg_timing_enable(0)
+    lib.ogg_timing_reset()
+    for other in results[1:]:
+        for u, v in zip(results[0], other):
+            assert u.shape == v.shape and (u.view(np.int64) == v.view(np.int64)).all()

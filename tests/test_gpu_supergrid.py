@@ -66,6 +66,86 @@ def test_cli_writes_reference_layout(SG, golden_configs, tmp_path):
         assert (tmp_path / ("ocean_hgrid_res4.0.nc" + sub + ".nc")).exists()
 
 
+def _check_values(lines):
+    """{label: tuple of floats} from the reference-format CHECK_metrics lines (labels repeat: keep them in order)."""
+    import re
+    out = []
+    for ln in lines:
+        if "CHECK_metrics" not in ln:
+            continue
+        label = ln.strip().split(":")[0]
+        nums = re.findall(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?", ln.split(")", 1)[1].replace("np.float64", ""))
+        out.append((label, tuple(float(v) for v in nums)))
+    return out
+
+
+@pytest.mark.parametrize("name", ["res4.0", "res1.0", "res1.0_dp", "res1.0_cutso", "readme_dp", "res0.5_equenh"])
+def test_cli_check_lines_match_reference(SG, golden_configs, name, tmp_path, capsys):
+    """main()'s self-check lines (OGG:1016, 1069, 1111, 1156, 1172) are part of the CLI's stdout: same lines, same order
+    (Mercator, bipolar cap, Southern Ocean, southern cap) as the unmodified reference printed for the recipe, the sums within
+    1e-12 relative (numpy's pairwise order is not reproduced), i.e. the percentages within 2e-10.  Covers the displaced-pole
+    line, which needs the rows inside the doughnut that the stitched grid never holds, the regular cap (its own top dx row)
+    and a Southern Ocean band that is cut afterwards."""
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    cfg = golden_configs[name]
+    G.cli(["-f", str(tmp_path / "g.nc")] + cfg["flags"].split())
+    got = _check_values(capsys.readouterr().out.splitlines())
+    want = _check_values(cfg["stdout_checks"])
+    assert [g[0] for g in got] == [w[0] for w in want]
+    for (label, gv), (_, wv) in zip(got, want):
+        assert len(gv) == len(wv), (label, gv, wv)
+        for g, w in zip(gv, wv):
+            assert abs(g - w) <= 2e-10 + 1e-9 * abs(w), (name, label, gv, wv)
+
+
+def test_write_nc_device_path_equals_host_path(SG, tmp_path):
+    """write_nc on device tensors (byte order reversed on the GPU, streamed through pinned staging in chunks) writes the
+    same file, byte for byte, as write_nc on the copied-out numpy arrays (host conversion) -- including a variable larger
+    than one staging chunk and odd element counts."""
+    import torch
+    from ocean_model_grid_generator_b200 import device as D, ocean_grid_generator as G
+    plan = SG.plan_supergrid(**_plan_args(_args("-r 1 --r_dp 0.2")))
+    a = SG.build_supergrid(plan).arrays()
+    h = {k: D.to_host(v) for k, v in a.items()}
+    old = G._DeviceVariable.CHUNK
+    try:
+        G._DeviceVariable.CHUNK = 100003          # several chunks per variable, not a multiple of anything
+        G._STAGING.clear()
+        G.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], fnam=str(tmp_path / "dev.nc"),
+                   description="d", history="h", source="s")
+    finally:
+        G._DeviceVariable.CHUNK = old
+        G._STAGING.clear()
+    G.write_nc(h["x"], h["y"], h["dx"], h["dy"], h["area"], h["angle_dx"], fnam=str(tmp_path / "host.nc"),
+               description="d", history="h", source="s")
+    assert (tmp_path / "dev.nc").read_bytes() == (tmp_path / "host.nc").read_bytes()
+    # ogg_bswap64 itself, device -> device
+    t = torch.arange(1000, dtype=torch.float64, device="cuda") * 1.25 - 7
+    out = torch.empty(1000, dtype=torch.int64, device="cuda")
+    from ocean_model_grid_generator_b200 import _cabi
+    _cabi.call("ogg_bswap64", D.ptr(t), D.ptr(out), 1000, D.stream())
+    assert out.cpu().numpy().tobytes() == t.cpu().numpy().astype(">f8").tobytes()
+
+
+def test_subgrid_files_follow_reference_cut_order(SG, golden_configs, tmp_path):
+    """--write_subgrid_files (OGG:1020, 1074, 1115, 1228): Mercator / bipolar / Southern Ocean files hold the sub-grids as
+    generated, the southern-cap file the cap after the doughnut cut, all BEFORE the south cut of the stitched grid."""
+    from scipy.io import netcdf_file
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    out = tmp_path / "g.nc"
+    G.cli(["-f", str(out), "-r", "1.0", "--r_dp", "0.2", "--south_cutoff_row", "45", "--write_subgrid_files", "--no_changing_meta"])
+    shapes = {}
+    for sub in ("Merc", "BP", "SO", "SC"):
+        f = netcdf_file(str(out) + sub + ".nc", "r", mmap=False)
+        shapes[sub] = f.variables["x"].shape
+        f.close()
+    f = netcdf_file(str(out), "r", mmap=False)
+    whole = f.variables["x"].shape
+    f.close()
+    assert shapes["SO"] == (56, 721) and shapes["SC"] == (35, 721) and shapes["BP"] == (121, 721)   # uncut SO; SC: 71 rows - 36 cut
+    assert whole == tuple(golden_configs["res1.0_cutso"]["arrays"]["x"]["shape"])                  # SC gone, 9 SO rows cut
+
+
 def test_reference_file_hash_res4_0_stretch(SG, tmp_path):
     """The reference's own known-answer test (t/test_ocean_grid_gen.py:25-46): sha256 of the whole file written by
     `-r 0.25 --ensure_nj_even --no_changing_meta`.  Those hashes were made with upstream numpypi's polynomials and

@@ -337,3 +337,25 @@ def test_netcdf3_writer_bytes_known_answer(tmp_path):
     netcdf3.write_supergrid(out, a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], global_attrs=gatts)
     assert out.read_bytes() == expected(gatts)
     assert len(out.read_bytes()) % 4 == 0
+
+
+def test_oracle_slab_composition_equals_whole(oracle):
+    """bench.py's CPU arm at N > 1 times ONE rank's row-slab share of the grid (oracle/supergrid_cpu.build_cpu(slab=...)),
+    composed through the reference's own decomposition of the cap metrics (index vectors -> h samples -> cell sums).
+    That route with a single slab is bit-identical to the whole-cap calls, and 3 slabs cover the grid exactly once."""
+    import numpy as np
+    import supergrid_cpu
+    from util import assert_bits
+    kw = dict(r=1.0, r_dp=0.2, south_cutoff_row=2)
+    whole = supergrid_cpu.build_cpu(**kw)
+    one = supergrid_cpu.build_cpu(slab=(0, 1), **kw)
+    for k in whole:
+        assert_bits(one[k], whole[k], "slab route " + k)
+    parts = [supergrid_cpu.build_cpu(slab=(g, 3), **kw) for g in range(3)]
+    assert sum(p["area"].shape[0] for p in parts) == whole["area"].shape[0]
+    tot = whole["area"].sum()
+    assert abs(sum(p["area"].sum() for p in parts) - tot) <= 1e-14 * tot
+    # every row of every slab is a row of the whole grid (set comparison on the row bytes of the area array)
+    rows = {whole["area"][j].tobytes() for j in range(whole["area"].shape[0])}
+    for p in parts:
+        assert all(p["area"][j].tobytes() in rows for j in range(p["area"].shape[0]))
