@@ -70,6 +70,16 @@ int ogg_phi_mercator(const double* y, int64_t n, double y_first, double R, doubl
  * dy [nyp-1][nxp]; area [nyp-1][nxp-1]. */
 int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int64_t nxp, double Re, int flags,
                           double* x, double* y, double* dx, double* dy, double* area, double* angle, void* stream);
+/* Several bands in ONE persistent launch (the Southern Ocean and Mercator bands of a supergrid step, plus a regular
+ * southern cap): same outputs per band as ogg_band_fill_metrics.  `bands` is a HOST array of nbands <= 4 descriptors
+ * whose pointers are device pointers. */
+typedef struct {
+  const double *lam, *phi;
+  int64_t nyp, nxp;
+  int flags;
+  double *x, *y, *dx, *dy, *area, *angle;
+} ogg_band_t;
+int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, void* stream);
 /* generate_grid_metrics_MIDAS (OGG:687-716) on a supplied mesh.  halo_x/halo_y (both or neither; [nxp]) are
  * the mesh row that follows row nyp-1 on the next row-slab; when given, dy and area get nyp rows instead of
  * nyp-1. */

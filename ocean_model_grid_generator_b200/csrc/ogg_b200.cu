@@ -260,58 +260,127 @@ __global__ void __launch_bounds__(256) k_band_tables(const double* __restrict__ 
   }
 }
 
-constexpr int kBandRows = 8;
-__global__ void __launch_bounds__(256) k_band_fill(const double* __restrict__ lam, const double* __restrict__ phi,
-                                                   const double* __restrict__ dxi, const double* __restrict__ hx,
-                                                   const double* __restrict__ xd, const double* __restrict__ cl,
-                                                   const double* __restrict__ cy, const double* __restrict__ dyr,
-                                                   const double* __restrict__ dsl, i64 nyp, i64 nxp, i64 nyp_v,
-                                                   double Re, double Re2, int metrics, double* __restrict__ x,
-                                                   double* __restrict__ y, double* __restrict__ dx,
-                                                   double* __restrict__ dy, double* __restrict__ area,
-                                                   double* __restrict__ angle) {
-  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
-  if (i >= nxp) return;
-  const i64 nx = nxp - 1;
-  const bool cell = i < nx;
-  const double lamv = lam[i], xdv = xd[i];
-  const double dxiv = cell ? dxi[i] : 0.0, hxv = cell ? hx[i] : 0.0;
-  const i64 jb = (i64)blockIdx.y * kBandRows;
+// One persistent launch fills every band of a step.  The flat vertex range of all bands together is cut into equal
+// shares, one per CTA (a multiple of the SM count: no partial wave, no tail); a CTA walks the rows of its share.  Within
+// a row a thread owns two adjacent columns chosen so that its 16-byte store is aligned -- per array family, because the
+// row length is odd for one family and even for the other, so the alignment of a row's first element alternates:
+//   family A (row length nxp): x, y, angle_dx, dy        family B (row length nxp-1): dx, area
+// and the one column that may precede the first aligned pair of a row is stored by the last thread as a scalar.
+// Nothing here changes a bit of any value (same expressions as before); only who stores what.
+struct BandDesc {
+  const double *lam, *phi, *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
+  double *x, *y, *dx, *dy, *area, *angle;
+  i64 nyp, nxp, nyp_v, v_begin;   // v_begin: flat index of the band's first vertex in the batch
+  int metrics;
+};
+constexpr int kMaxBands = 4;
+struct BandBatch { BandDesc b[kMaxBands]; int n; i64 total; double Re, Re2; };
+
+OGG_DI void store_pair(double* q, double v0, double v1, bool has0, bool has1) {
+  if (has0 && has1) *reinterpret_cast<double2*>(q) = make_double2(v0, v1);   // q is 16-byte aligned by construction
+  else if (has0) q[0] = v0;
+  else if (has1) q[1] = v1;
+}
+OGG_DI double band_angle(double xdv, double cyj, double dyc, double ang_pos, double ang_neg) {
   // angle_x on a band (:725-728): y[ia]-y[ib] = phi-phi = +0, so p_atan2 takes its ay == 0 branch: +0 for a
   // non-negative second argument, pi - (0 - pi_lo) for a negative one -- two constants; anything else (NaN) goes
-  // through the general code.  Same for dx (:698): dy_i = +0 and sqrt(0 + tt*tt) = |tt|.  Nothing here changes a bit; it only keeps the per-vertex work to a handful of multiplies so
-  // that the kernel is bound by its 48 B/vertex of stores.
+  // through the general code.
+  const double arg = xdv * cyj;
+  if (dyc == 0.0 && arg >= 0.0) return ang_pos;
+  if (dyc == 0.0 && arg < 0.0) return ang_neg;
+  return p_atan2(dyc, arg) / kPi180;
+}
+OGG_DI double band_dx(double dxiv, double clj, double dyc, double Re) {
+  // dx (:698): dy_i = +0 and sqrt(0 + tt*tt) = |tt|: sqrt(fl(t*t)) == |t| in binary floating point, round-to-nearest,
+  // when t*t neither under- nor overflows (Boldo 2015); checked on 1e7 values in
+  // tests/test_oracle_cpu.py::test_sqrt_of_square_identity
+  const double dy_i = dyc * kPi180;
+  const double tt = dxiv * clj;
+  const double t2 = tt * tt;
+  const double root = (dy_i == 0.0 && t2 >= 0x1p-1000 && t2 <= 0x1p1000) ? fabs(tt) : sqrt(dy_i * dy_i + t2);
+  return Re * root;
+}
+constexpr int kBandThreads = 256;
+__global__ void __launch_bounds__(kBandThreads) k_band_fill(const __grid_constant__ BandBatch B) {
+  const i64 share = (B.total + gridDim.x - 1) / gridDim.x;
+  i64 v = (i64)blockIdx.x * share;
+  const i64 v_end = v + share < B.total ? v + share : B.total;
   const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
-#pragma unroll
-  for (int r = 0; r < kBandRows; ++r) {
-    const i64 j = jb + r;
-    if (j >= nyp) break;
-    const double phij = phi[j];
-    const double dyc = phij - phij;  // y[ia]-y[ib] on a band: +0 unless phi is not finite
-    if (j < nyp_v) {
-      if (x) x[j * nxp + i] = lamv;
-      if (y) y[j * nxp + i] = phij;
-      if (angle) {
-        const double arg = xdv * cy[j];
-        double a;
-        if (dyc == 0.0 && arg >= 0.0) a = ang_pos;
-        else if (dyc == 0.0 && arg < 0.0) a = ang_neg;
-        else a = p_atan2(dyc, arg) / kPi180;
-        angle[j * nxp + i] = a;
-      }
-      if (metrics && cell && dx) {
-        const double dy_i = dyc * kPi180;
-        const double tt = dxiv * cl[j];
-        const double t2 = tt * tt;
-        // sqrt(fl(t*t)) == |t| in binary floating point, round-to-nearest, when t*t neither under- nor overflows
-        // (Boldo 2015); checked on 1e7 values in tests/test_oracle_cpu.py::test_sqrt_of_square_identity
-        const double root = (dy_i == 0.0 && t2 >= 0x1p-1000 && t2 <= 0x1p1000) ? fabs(tt) : sqrt(dy_i * dy_i + t2);
-        dx[j * nx + i] = Re * root;
+  while (v < v_end) {
+    int k = 0;
+    while (k + 1 < B.n && v >= B.b[k + 1].v_begin) ++k;
+    const BandDesc& D = B.b[k];
+    const i64 nxp = D.nxp, nx = nxp - 1;
+    const i64 j = (v - D.v_begin) / nxp;
+    const i64 ia = (v - D.v_begin) - j * nxp;                       // first column of this row in the share
+    const i64 row_end = D.v_begin + (j + 1) * nxp;
+    const i64 ib = (row_end < v_end ? row_end : v_end) - (D.v_begin + j * nxp);   // one past the last column
+    v = D.v_begin + j * nxp + ib;
+    // per-row quantities (uniform over the CTA)
+    const double phij = D.phi[j];
+    const double dyc = phij - phij;                                   // y[ia]-y[ib] on a band: +0 unless phi is not finite
+    const bool vrow = j < D.nyp_v, crow = D.metrics && j < D.nyp - 1, mrow = D.metrics && vrow;
+    const double cyj = D.cy[j], clj = D.cl[j];
+    const double dyrj = crow ? D.dyr[j] : 0.0, dslj = crow ? D.dsl[j] : 0.0;
+    // family A: columns [ia, ib) of row j, row length nxp.  Pairs start at the first column whose address is 16-byte
+    // aligned (the arrays of a family share their alignment; checked on the host, else the scalar path is taken).
+    {
+      double* xr = D.x ? D.x + j * nxp : nullptr;
+      double* yr = D.y ? D.y + j * nxp : nullptr;
+      double* ar = D.angle ? D.angle + j * nxp : nullptr;
+      double* dr = D.dy ? D.dy + j * nxp : nullptr;
+      const double* any = xr ? xr : (yr ? yr : (ar ? ar : dr));
+      const i64 odd = any ? (i64)((reinterpret_cast<unsigned long long>(any + ia) >> 3) & 1ull) : 0;
+      // thread t owns columns c, c+1 with c = ia - odd... : when `odd`, the pair straddles ia-1 | ia and only ia is stored
+      for (i64 c = ia - odd + 2 * (i64)threadIdx.x; c < ib; c += 2 * kBandThreads) {
+        const bool h0 = c >= ia, h1 = c + 1 < ib;
+        const i64 c0 = h0 ? c : c + 1, c1 = h1 ? c + 1 : c;           // clamped table indices
+        if (vrow) {
+          if (xr) store_pair(xr + c, D.lam[c0], D.lam[c1], h0, h1);
+          if (yr) store_pair(yr + c, phij, phij, h0, h1);
+          if (ar) store_pair(ar + c, band_angle(D.xd[c0], cyj, dyc, ang_pos, ang_neg), band_angle(D.xd[c1], cyj, dyc, ang_pos, ang_neg), h0, h1);
+        }
+        if (crow && dr) store_pair(dr + c, dyrj, dyrj, h0, h1);
       }
     }
-    if (metrics && j < nyp - 1) {
-      if (dy) dy[j * nxp + i] = dyr[j];
-      if (cell && area) area[j * nx + i] = Re2 * (hxv * dsl[j]);
+    // family B: columns [ia, min(ib, nx)) of row j, row length nx
+    if ((mrow && D.dx) || (crow && D.area)) {
+      const i64 ibb = ib < nx ? ib : nx;
+      double* dxr = (mrow && D.dx) ? D.dx + j * nx : nullptr;
+      double* arr = (crow && D.area) ? D.area + j * nx : nullptr;
+      const double* any = dxr ? dxr : arr;
+      const i64 odd = (i64)((reinterpret_cast<unsigned long long>(any + ia) >> 3) & 1ull);
+      for (i64 c = ia - odd + 2 * (i64)threadIdx.x; c < ibb; c += 2 * kBandThreads) {
+        const bool h0 = c >= ia, h1 = c + 1 < ibb;
+        const i64 c0 = h0 ? c : c + 1, c1 = h1 ? c + 1 : c;
+        if (dxr) store_pair(dxr + c, band_dx(D.dxi[c0], clj, dyc, B.Re), band_dx(D.dxi[c1], clj, dyc, B.Re), h0, h1);
+        if (arr) store_pair(arr + c, B.Re2 * (D.hx[c0] * dslj), B.Re2 * (D.hx[c1] * dslj), h0, h1);
+      }
+    }
+  }
+}
+// all-scalar variant: taken when the arrays of a family do not share their 16-byte alignment (never for buffers laid out
+// like the supergrid's; any caller-supplied pointers are legal)
+__global__ void __launch_bounds__(kBandThreads) k_band_fill_scalar(const __grid_constant__ BandBatch B) {
+  const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
+  for (i64 v = blockIdx.x * (i64)blockDim.x + threadIdx.x; v < B.total; v += (i64)gridDim.x * blockDim.x) {
+    int k = 0;
+    while (k + 1 < B.n && v >= B.b[k + 1].v_begin) ++k;
+    const BandDesc& D = B.b[k];
+    const i64 nxp = D.nxp, nx = nxp - 1;
+    const i64 j = (v - D.v_begin) / nxp, i = (v - D.v_begin) - j * nxp;
+    const double phij = D.phi[j];
+    const double dyc = phij - phij;
+    const bool cell = i < nx;
+    if (j < D.nyp_v) {
+      if (D.x) D.x[j * nxp + i] = D.lam[i];
+      if (D.y) D.y[j * nxp + i] = phij;
+      if (D.angle) D.angle[j * nxp + i] = band_angle(D.xd[i], D.cy[j], dyc, ang_pos, ang_neg);
+      if (D.metrics && cell && D.dx) D.dx[j * nx + i] = band_dx(D.dxi[i], D.cl[j], dyc, B.Re);
+    }
+    if (D.metrics && j < D.nyp - 1) {
+      if (D.dy) D.dy[j * nxp + i] = D.dyr[j];
+      if (cell && D.area) D.area[j * nx + i] = B.Re2 * (D.hx[i] * D.dsl[j]);
     }
   }
 }
@@ -1539,24 +1608,58 @@ int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* 
   return OGG_OK;
 }
 
-int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int64_t nxp, double Re, int flags,
-                          double* x, double* y, double* dx, double* dy, double* area, double* angle, void* stream) {
-  if (!lam || !phi || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
+int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, void* stream) {
+  if (!bands || nbands < 1 || nbands > kMaxBands) return OGG_ERR_ARG;
   cudaStream_t st = S(stream);
   Scratch ws(st);
-  double *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
-  OGG_CUDA(ws.get(&dxi, nxp)); OGG_CUDA(ws.get(&hx, nxp)); OGG_CUDA(ws.get(&xd, nxp));
-  OGG_CUDA(ws.get(&cl, nyp)); OGG_CUDA(ws.get(&cy, nyp)); OGG_CUDA(ws.get(&dyr, nyp)); OGG_CUDA(ws.get(&dsl, nyp));
-  const i64 m = nxp > nyp ? nxp : nyp;
-  OGG_LAUNCH(KID_BAND_TABLES, (k_band_tables), (cdiv_u(m, 256), 256), (st), lam, phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
-  OGG_LAUNCH_CHECK();
-  const i64 nyp_v = (flags & OGG_BAND_SKIP_TOP_VERTEX_ROW) ? nyp - 1 : nyp;
-  const int metrics = (flags & OGG_BAND_NO_METRICS) ? 0 : 1;
-  dim3 g(cdiv_u(nxp, 256), cdiv_u(nyp, kBandRows));
-  OGG_LAUNCH(KID_BAND_FILL, (k_band_fill), (g, 256), (st), lam, phi, dxi, hx, xd, cl, cy, dyr, dsl, nyp, nxp, nyp_v, Re, Re * Re, metrics, x, y, dx,
-                                 dy, area, angle);
+  BandBatch B;
+  B.n = nbands; B.Re = Re; B.Re2 = Re * Re; B.total = 0;
+  bool vector_ok = true;
+  for (int k = 0; k < nbands; ++k) {
+    const ogg_band_t& a = bands[k];
+    if (!a.lam || !a.phi || a.nyp < 1 || a.nxp < 2) return OGG_ERR_ARG;
+    const i64 nyp = a.nyp, nxp = a.nxp;
+    double *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
+    OGG_CUDA(ws.get(&dxi, nxp)); OGG_CUDA(ws.get(&hx, nxp)); OGG_CUDA(ws.get(&xd, nxp));
+    OGG_CUDA(ws.get(&cl, nyp)); OGG_CUDA(ws.get(&cy, nyp)); OGG_CUDA(ws.get(&dyr, nyp)); OGG_CUDA(ws.get(&dsl, nyp));
+    const i64 m = nxp > nyp ? nxp : nyp;
+    OGG_LAUNCH(KID_BAND_TABLES, (k_band_tables), (cdiv_u(m, 256), 256), (st), a.lam, a.phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
+    OGG_LAUNCH_CHECK();
+    BandDesc& D = B.b[k];
+    D.lam = a.lam; D.phi = a.phi; D.dxi = dxi; D.hx = hx; D.xd = xd; D.cl = cl; D.cy = cy; D.dyr = dyr; D.dsl = dsl;
+    D.x = a.x; D.y = a.y; D.dx = a.dx; D.dy = a.dy; D.area = a.area; D.angle = a.angle;
+    D.nyp = nyp; D.nxp = nxp;
+    D.nyp_v = (a.flags & OGG_BAND_SKIP_TOP_VERTEX_ROW) ? nyp - 1 : nyp;
+    D.metrics = (a.flags & OGG_BAND_NO_METRICS) ? 0 : 1;
+    D.v_begin = B.total;
+    B.total += nyp * nxp;
+    // the vector path assumes that the arrays of a family share their alignment modulo 16 bytes
+    auto par = [](const double* q) { return (reinterpret_cast<unsigned long long>(q) >> 3) & 1ull; };
+    const double* famA[4] = {a.x, a.y, a.angle, a.dy};
+    const double* famB[2] = {a.dx, a.area};
+    const double *fa = nullptr, *fb = nullptr;
+    for (const double* q : famA) { if (!q) continue; if (!fa) fa = q; else if (par(q) != par(fa)) vector_ok = false; }
+    for (const double* q : famB) { if (!q) continue; if (!fb) fb = q; else if (par(q) != par(fb)) vector_ok = false; }
+  }
+  // persistent grid: a multiple of the SM count, each CTA an equal share of the flat vertex range (at least a few
+  // hundred vertices per CTA so that tiny bands do not launch idle CTAs)
+  i64 ctas = (i64)num_sms() * 8;
+  const i64 max_useful = (B.total + 511) / 512;
+  if (ctas > max_useful) ctas = max_useful < 1 ? 1 : max_useful;
+  launch_begin(KID_BAND_FILL, st);
+  if (vector_ok) k_band_fill<<<(unsigned)ctas, kBandThreads, 0, st>>>(B);
+  else k_band_fill_scalar<<<(unsigned)ctas, kBandThreads, 0, st>>>(B);
+  launch_end(st);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
+}
+
+int ogg_band_fill_metrics(const double* lam, const double* phi, int64_t nyp, int64_t nxp, double Re, int flags,
+                          double* x, double* y, double* dx, double* dy, double* area, double* angle, void* stream) {
+  ogg_band_t b;
+  b.lam = lam; b.phi = phi; b.nyp = nyp; b.nxp = nxp; b.flags = flags;
+  b.x = x; b.y = y; b.dx = dx; b.dy = dy; b.area = area; b.angle = angle;
+  return ogg_band_fill_metrics_batch(&b, 1, Re, stream);
 }
 
 int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp, double Re, int areafix,
