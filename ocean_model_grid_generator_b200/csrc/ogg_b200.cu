@@ -260,27 +260,22 @@ __global__ void __launch_bounds__(256) k_band_tables(const double* __restrict__ 
   }
 }
 
-// One persistent launch fills every band of a step.  The flat vertex range of all bands together is cut into equal
-// shares, one per CTA (a multiple of the SM count: no partial wave, no tail); a CTA walks the rows of its share.  Within
-// a row a thread owns two adjacent columns chosen so that its 16-byte store is aligned -- per array family, because the
-// row length is odd for one family and even for the other, so the alignment of a row's first element alternates:
-//   family A (row length nxp): x, y, angle_dx, dy        family B (row length nxp-1): dx, area
-// and the one column that may precede the first aligned pair of a row is stored by the last thread as a scalar.
-// Nothing here changes a bit of any value (same expressions as before); only who stores what.
+// One launch fills every band of a step: blockIdx.y runs over the row tiles of all bands, one thread per column, R rows
+// per CTA (host-chosen so that the grid is close to a whole number of waves of resident CTAs -- at -r 4 the fixed
+// 8-row tiles of round 1 left the second wave 78 % full).  A thread keeps the column-only factors in registers; the
+// row-only factors are uniform loads.  Stores are plain 8-byte stores, a warp writing 256 contiguous bytes per array and
+// row: 16-byte pair stores (which need a per-row alignment shift because the row length nxp is odd) and column strips
+// with a one-wave persistent grid were both measured slower (DESIGN.md "tried and rejected").
 struct BandDesc {
   const double *lam, *phi, *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
   double *x, *y, *dx, *dy, *area, *angle;
-  i64 nyp, nxp, nyp_v, v_begin;   // v_begin: flat index of the band's first vertex in the batch
+  i64 nyp, nxp, nyp_v;
+  i64 t_begin;                    // first row tile (blockIdx.y) of this band
   int metrics;
 };
 constexpr int kMaxBands = 4;
-struct BandBatch { BandDesc b[kMaxBands]; int n; i64 total; double Re, Re2; };
+struct BandBatch { BandDesc b[kMaxBands]; int n; i64 rows_per_tile; double Re, Re2; };
 
-OGG_DI void store_pair(double* q, double v0, double v1, bool has0, bool has1) {
-  if (has0 && has1) *reinterpret_cast<double2*>(q) = make_double2(v0, v1);   // q is 16-byte aligned by construction
-  else if (has0) q[0] = v0;
-  else if (has1) q[1] = v1;
-}
 OGG_DI double band_angle(double xdv, double cyj, double dyc, double ang_pos, double ang_neg) {
   // angle_x on a band (:725-728): y[ia]-y[ib] = phi-phi = +0, so p_atan2 takes its ay == 0 branch: +0 for a
   // non-negative second argument, pi - (0 - pi_lo) for a negative one -- two constants; anything else (NaN) goes
@@ -302,85 +297,44 @@ OGG_DI double band_dx(double dxiv, double clj, double dyc, double Re) {
 }
 constexpr int kBandThreads = 256;
 __global__ void __launch_bounds__(kBandThreads) k_band_fill(const __grid_constant__ BandBatch B) {
-  const i64 share = (B.total + gridDim.x - 1) / gridDim.x;
-  i64 v = (i64)blockIdx.x * share;
-  const i64 v_end = v + share < B.total ? v + share : B.total;
+  int k = 0;
+  while (k + 1 < B.n && (i64)blockIdx.y >= B.b[k + 1].t_begin) ++k;
+  const double* __restrict__ lam = B.b[k].lam;
+  const double* __restrict__ phi = B.b[k].phi;
+  const double* __restrict__ cl = B.b[k].cl;
+  const double* __restrict__ cy = B.b[k].cy;
+  const double* __restrict__ dyr = B.b[k].dyr;
+  const double* __restrict__ dsl = B.b[k].dsl;
+  double* __restrict__ x = B.b[k].x;
+  double* __restrict__ y = B.b[k].y;
+  double* __restrict__ dx = B.b[k].dx;
+  double* __restrict__ dy = B.b[k].dy;
+  double* __restrict__ area = B.b[k].area;
+  double* __restrict__ angle = B.b[k].angle;
+  const i64 nxp = B.b[k].nxp, nx = nxp - 1, nyp = B.b[k].nyp, nyp_v = B.b[k].nyp_v;
+  const int metrics = B.b[k].metrics;
+  const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (i >= nxp) return;
+  const bool cell = i < nx;
+  const double lamv = lam[i], xdv = B.b[k].xd[i];
+  const double dxiv = cell ? B.b[k].dxi[i] : 0.0, hxv = cell ? B.b[k].hx[i] : 0.0;
+  const i64 j0 = ((i64)blockIdx.y - B.b[k].t_begin) * B.rows_per_tile;
+  const i64 j1 = j0 + B.rows_per_tile < nyp ? j0 + B.rows_per_tile : nyp;
   const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
-  while (v < v_end) {
-    int k = 0;
-    while (k + 1 < B.n && v >= B.b[k + 1].v_begin) ++k;
-    const BandDesc& D = B.b[k];
-    const i64 nxp = D.nxp, nx = nxp - 1;
-    const i64 j = (v - D.v_begin) / nxp;
-    const i64 ia = (v - D.v_begin) - j * nxp;                       // first column of this row in the share
-    const i64 row_end = D.v_begin + (j + 1) * nxp;
-    const i64 ib = (row_end < v_end ? row_end : v_end) - (D.v_begin + j * nxp);   // one past the last column
-    v = D.v_begin + j * nxp + ib;
-    // per-row quantities (uniform over the CTA)
-    const double phij = D.phi[j];
-    const double dyc = phij - phij;                                   // y[ia]-y[ib] on a band: +0 unless phi is not finite
-    const bool vrow = j < D.nyp_v, crow = D.metrics && j < D.nyp - 1, mrow = D.metrics && vrow;
-    const double cyj = D.cy[j], clj = D.cl[j];
-    const double dyrj = crow ? D.dyr[j] : 0.0, dslj = crow ? D.dsl[j] : 0.0;
-    // family A: columns [ia, ib) of row j, row length nxp.  Pairs start at the first column whose address is 16-byte
-    // aligned (the arrays of a family share their alignment; checked on the host, else the scalar path is taken).
-    {
-      double* xr = D.x ? D.x + j * nxp : nullptr;
-      double* yr = D.y ? D.y + j * nxp : nullptr;
-      double* ar = D.angle ? D.angle + j * nxp : nullptr;
-      double* dr = D.dy ? D.dy + j * nxp : nullptr;
-      const double* any = xr ? xr : (yr ? yr : (ar ? ar : dr));
-      const i64 odd = any ? (i64)((reinterpret_cast<unsigned long long>(any + ia) >> 3) & 1ull) : 0;
-      // thread t owns columns c, c+1 with c = ia - odd... : when `odd`, the pair straddles ia-1 | ia and only ia is stored
-      for (i64 c = ia - odd + 2 * (i64)threadIdx.x; c < ib; c += 2 * kBandThreads) {
-        const bool h0 = c >= ia, h1 = c + 1 < ib;
-        const i64 c0 = h0 ? c : c + 1, c1 = h1 ? c + 1 : c;           // clamped table indices
-        if (vrow) {
-          if (xr) store_pair(xr + c, D.lam[c0], D.lam[c1], h0, h1);
-          if (yr) store_pair(yr + c, phij, phij, h0, h1);
-          if (ar) store_pair(ar + c, band_angle(D.xd[c0], cyj, dyc, ang_pos, ang_neg), band_angle(D.xd[c1], cyj, dyc, ang_pos, ang_neg), h0, h1);
-        }
-        if (crow && dr) store_pair(dr + c, dyrj, dyrj, h0, h1);
-      }
+  const double Re = B.Re, Re2 = B.Re2;
+#pragma unroll 4
+  for (i64 j = j0; j < j1; ++j) {
+    const double phij = phi[j];
+    const double dyc = phij - phij;  // y[ia]-y[ib] on a band: +0 unless phi is not finite
+    if (j < nyp_v) {
+      if (x) x[j * nxp + i] = lamv;
+      if (y) y[j * nxp + i] = phij;
+      if (angle) angle[j * nxp + i] = band_angle(xdv, cy[j], dyc, ang_pos, ang_neg);
+      if (metrics && cell && dx) dx[j * nx + i] = band_dx(dxiv, cl[j], dyc, Re);
     }
-    // family B: columns [ia, min(ib, nx)) of row j, row length nx
-    if ((mrow && D.dx) || (crow && D.area)) {
-      const i64 ibb = ib < nx ? ib : nx;
-      double* dxr = (mrow && D.dx) ? D.dx + j * nx : nullptr;
-      double* arr = (crow && D.area) ? D.area + j * nx : nullptr;
-      const double* any = dxr ? dxr : arr;
-      const i64 odd = (i64)((reinterpret_cast<unsigned long long>(any + ia) >> 3) & 1ull);
-      for (i64 c = ia - odd + 2 * (i64)threadIdx.x; c < ibb; c += 2 * kBandThreads) {
-        const bool h0 = c >= ia, h1 = c + 1 < ibb;
-        const i64 c0 = h0 ? c : c + 1, c1 = h1 ? c + 1 : c;
-        if (dxr) store_pair(dxr + c, band_dx(D.dxi[c0], clj, dyc, B.Re), band_dx(D.dxi[c1], clj, dyc, B.Re), h0, h1);
-        if (arr) store_pair(arr + c, B.Re2 * (D.hx[c0] * dslj), B.Re2 * (D.hx[c1] * dslj), h0, h1);
-      }
-    }
-  }
-}
-// all-scalar variant: taken when the arrays of a family do not share their 16-byte alignment (never for buffers laid out
-// like the supergrid's; any caller-supplied pointers are legal)
-__global__ void __launch_bounds__(kBandThreads) k_band_fill_scalar(const __grid_constant__ BandBatch B) {
-  const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
-  for (i64 v = blockIdx.x * (i64)blockDim.x + threadIdx.x; v < B.total; v += (i64)gridDim.x * blockDim.x) {
-    int k = 0;
-    while (k + 1 < B.n && v >= B.b[k + 1].v_begin) ++k;
-    const BandDesc& D = B.b[k];
-    const i64 nxp = D.nxp, nx = nxp - 1;
-    const i64 j = (v - D.v_begin) / nxp, i = (v - D.v_begin) - j * nxp;
-    const double phij = D.phi[j];
-    const double dyc = phij - phij;
-    const bool cell = i < nx;
-    if (j < D.nyp_v) {
-      if (D.x) D.x[j * nxp + i] = D.lam[i];
-      if (D.y) D.y[j * nxp + i] = phij;
-      if (D.angle) D.angle[j * nxp + i] = band_angle(D.xd[i], D.cy[j], dyc, ang_pos, ang_neg);
-      if (D.metrics && cell && D.dx) D.dx[j * nx + i] = band_dx(D.dxi[i], D.cl[j], dyc, B.Re);
-    }
-    if (D.metrics && j < D.nyp - 1) {
-      if (D.dy) D.dy[j * nxp + i] = D.dyr[j];
-      if (cell && D.area) D.area[j * nx + i] = B.Re2 * (D.hx[i] * D.dsl[j]);
+    if (metrics && j < nyp - 1) {
+      if (dy) dy[j * nxp + i] = dyr[j];
+      if (cell && area) area[j * nx + i] = Re2 * (hxv * dsl[j]);
     }
   }
 }
@@ -507,7 +461,7 @@ OGG_DI BpCol bp_col(double lamg, double lon_bp) {
 }
 // M: division / square-root policy (ogg_trig.cuh); with MathFast the caller must redo the sample if !m.ok()
 template <bool FULL, class M>
-OGG_DI void bp_sample(M& m, const typename M::Divisor& pi180, const BpRow& R, const BpCol& C, double lon_bp, double rp,
+OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, double rp,
                       double& lams, double& phis, double& h_i_inv, double& h_j_inv) {
   const double alpha2 = C.alpha2, beta2_inv = R.beta2_inv;
   const double rden = m.div_num_ok(1.0, 1.0 + alpha2 * beta2_inv);  // :47
@@ -515,7 +469,7 @@ OGG_DI void bp_sample(M& m, const typename M::Divisor& pi180, const BpRow& R, co
   if (FULL) {
     double B = C.sinla * m.sqrt_(rden);                  // :50
     if (huge) B = 0.0;                                   // :52
-    double lamc = m.div_by(p_asin(m, B), pi180);         // :53
+    double lamc = m.div_pi180(p_asin(m, B));             // :53
     const double dl = C.dl;
     if (dl > 90 && dl <= 180) lamc = 180 - lamc;         // :58
     if (dl > 180 && dl <= 270) lamc = 180 + lamc;        // :59
@@ -528,10 +482,10 @@ OGG_DI void bp_sample(M& m, const typename M::Divisor& pi180, const BpRow& R, co
   const double chic = p_acos(m, A);                      // :69
   const double tc = p_tan(m, chic / 2);
   const double q = rp * tc;
-  phis = 90 - m.div_by(2 * p_atan(m, q), pi180);         // :70
+  phis = 90 - m.div_pi180(2 * p_atan(m, q));             // :70
   const double rden2 = m.div_num_ok(1.0, 1 + q * q);     // :72
   const double M_inv = (rp * (1 + tc * tc)) * rden2;     // :73
-  const double cp = p_cos(phis * kPi180);
+  const double cp = p_cos(m, phis * kPi180);
   const double cos2phis = cp * cp;                       // :79
   const double MM = M_inv * M_inv, r2 = rden * rden;
   double hj = ((((cos2phis * alpha2) * (1 - alpha2)) * beta2_inv) * (1 + beta2_inv)) * r2 +
@@ -546,7 +500,7 @@ template <bool FULL>
 OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, double& lams, double& phis,
                       double& h_i_inv, double& h_j_inv) {
   MathIeee m;
-  bp_sample<FULL>(m, m.divisor(kPi180), R, C, lon_bp, rp, lams, phis, h_i_inv, h_j_inv);
+  bp_sample<FULL>(m, R, C, lon_bp, rp, lams, phis, h_i_inv, h_j_inv);
 }
 
 __global__ void __launch_bounds__(256) k_bp_projection(const double* __restrict__ lamg, const double* __restrict__ phig,
@@ -772,10 +726,10 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
   extern __shared__ double smem[];
   double* sx = smem;
   double* sy = smem + SR * SCP;
+  __shared__ __align__(16) double s_tab[kTabAlloc];
   const i64 gr0 = (i64)blockIdx.y * TR * (N - 1), gc0 = (i64)blockIdx.x * TC * (N - 1);
   const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
-  MathFast mf;
-  const MathFast::Divisor pi180 = mf.divisor(kPi180), dnx = mf.divisor((double)nx), dny = mf.divisor((double)ny);
+  MathFast mf(load_table<256>(s_tab, (double)nx, (double)ny));   // cached divisors: pi/180, nx, ny (all moderate: nx, ny >= 1)
   // one sample: scaled h_i_inv, h_j_inv of unique row r / column c of this tile -> shared memory
   auto sample = [&](int r, int c, const BpCol& C, bool col_ok) {
     const i64 gr = gr0 + r;
@@ -784,9 +738,9 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
       const BpRow R = rt[gr];
       double l, p;
       mf.reset();
-      bp_sample<false>(mf, pi180, R, C, lon_bp, rp, l, p, a, b);
-      a = mf.div_by((a * 2) * kPi, dnx);                                          // :131
-      b = mf.div_by((b * (90 - lat0_bp)) * kPi180, dny);                          // :132
+      bp_sample<false>(mf, R, C, lon_bp, rp, l, p, a, b);
+      a = mf.div_slot<1>((a * 2) * kPi);                                          // :131
+      b = mf.div_slot<2>((b * (90 - lat0_bp)) * kPi180);                          // :132
       if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, the lon_bp meridian)
         const HiHj o = bp_qsample_ieee(R, C, lon_bp, rp, lat0_bp, (double)nx, (double)ny);
         a = o.a; b = o.b;
@@ -919,18 +873,17 @@ OGG_DI Cx dp_col(double lon, Cx z0) {  // e2ithetaprime (:451-452), a function o
 }
 OGG_DI double dp_row(double lat, double r_joint) { return p_tan((90 + lat) * kPi180) / r_joint; }  // :448
 template <class M>
-OGG_DI void dp_vertex(M& m, const typename M::Divisor& pi180, double r, Cx ep, const DpConst& K, double& lam_raw,
-                      double& phi) {
+OGG_DI void dp_vertex(M& m, double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
   const Cx z = cmul(Cx{r, 0.0}, ep);                                                         // :454
   const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
   const Cx w = cdivn(m, Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, 0.0 + q.im});     // :455
   lam_raw = p_atan2(m, w.im, w.re) * kC[k180OverPi];                                          // :457
   const double rw = m.sqrt_(w.re * w.re + w.im * w.im);                                      // :465
-  phi = -90 + m.div_by(p_atan(m, rw * K.r_joint), pi180);                                    // :466
+  phi = -90 + m.div_pi180(p_atan(m, rw * K.r_joint));                                        // :466
 }
 OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
   MathIeee m;
-  dp_vertex(m, m.divisor(kPi180), r, ep, K, lam_raw, phi);
+  dp_vertex(m, r, ep, K, lam_raw, phi);
 }
 
 __global__ void k_dp_constants(double lat0, double lam_pole, double r_pole, double* __restrict__ out3) {
@@ -1054,8 +1007,8 @@ template <class M>
 OGG_DI double haversine(M& m, double lam0, double phi0, double lam1, double phi1) {
   const double l0 = lam0 * kPi180, p0 = phi0 * kPi180, l1 = lam1 * kPi180, p1 = phi1 * kPi180;
   const double dphi = p1 - p0, dlam = l1 - l0;
-  const double s1 = p_sin(0.5 * dphi), s2 = p_sin(0.5 * dlam);
-  const double d = s1 * s1 + ((s2 * s2) * p_cos(p0)) * p_cos(p1);  // :531
+  const double s1 = p_sin(m, 0.5 * dphi), s2 = p_sin(m, 0.5 * dlam);
+  const double d = s1 * s1 + ((s2 * s2) * p_cos(m, p0)) * p_cos(m, p1);  // :531
   return 2.0 * p_asin(m, m.sqrt_(d));                              // :532
 }
 OGG_DI double haversine(double lam0, double phi0, double lam1, double phi1) {
@@ -1090,8 +1043,8 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
 __device__ __noinline__ double haversine_ieee(double lam0, double phi0, double lam1, double phi1) {
   return haversine(lam0, phi0, lam1, phi1);
 }
-__device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
-  MathFast m;
+__device__ __noinline__ double haversine_ol(unsigned tab, double lam0, double phi0, double lam1, double phi1) {
+  MathFast m(tab);
   const double v = haversine(m, lam0, phi0, lam1, phi1);
   return m.ok() ? v : haversine_ieee(lam0, phi0, lam1, phi1);   // e.g. coincident points: sqrt(0), asin(0)
 }
@@ -1142,9 +1095,9 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
   __shared__ double phiS[NM][THREADS];
   __shared__ unsigned shw[2 * kWarps];
   __shared__ unsigned s_state;
+  __shared__ __align__(16) double s_tab[kTabAlloc];
   const DpConst K = dp_load(cst);
-  MathFast mf;
-  const MathFast::Divisor pi180 = mf.divisor(kPi180);
+  MathFast mf(load_table<THREADS>(s_tab));
   const i64 ntile = (ncol + TW - 1) / TW;
   const i64 nitem = nrow * ntile;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -1169,7 +1122,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];            // e' at i +- (lvl+1) eps (kinds 0,1) or i
         double l, p;
         mf.reset();
-        dp_vertex(mf, pi180, rv, ep, K, l, p);
+        dp_vertex(mf, rv, ep, K, l, p);
         if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, an axis crossing)
           const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
           l = o.l; p = o.p;
@@ -1230,7 +1183,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         double l0 = lamS[2 * q][threadIdx.x], l1 = lamS[2 * q + 1][threadIdx.x];
         if ((st >> (2 * q)) & 1u) l0 = l0 - 360;                           // :473
         if ((st >> (2 * q + 1)) & 1u) l1 = l1 - 360;
-        phiS[2 * q][threadIdx.x] = haversine_ol(l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
+        phiS[2 * q][threadIdx.x] = haversine_ol(mf.tab, l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
       }
       // pair 2m = i-direction at level m, pair 2m+1 = j-direction (:538-546, :553-561)
       hx[r * ncol + c] = fd_combine<2 * NV>(phiS[0][threadIdx.x], NV > 1 ? phiS[4][threadIdx.x] : 0.0,
@@ -1290,11 +1243,13 @@ OGG_DI double gen_operand(unsigned long long h, int mode) {
 // from the IEEE result; counts[2]: sets in MathFast's documented range that a guard rejected (must be 0 for modes != 1)
 __global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long long seed, int mode,
                                                           unsigned long long* __restrict__ counts) {
+  __shared__ __align__(16) double s_tab[kTabAlloc];
+  const unsigned tab = load_table<256>(s_tab);
   unsigned long long acc = 0, bad = 0, rej = 0;
   for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
     const unsigned long long h0 = splitmix64(seed + 2ull * (unsigned long long)e), h1 = splitmix64(h0 ^ 0x5851f42d4c957f2dull);
     const double a = gen_operand(h0, mode), b = gen_operand(h1, mode);
-    MathFast m;
+    MathFast m(tab);
     const double q = m.div(a, b);
     if (m.ok()) { ++acc; if (__double_as_longlong(q) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
     m.reset();
@@ -1303,7 +1258,7 @@ __global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long l
     m.reset();
     const MathFast::Divisor d = m.divisor(b);
     const double q2 = m.div_by(a, d);
-    if (m.ok()) { ++acc; if (__double_as_longlong(q2) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
+    if (m.ok() && d.valid) { ++acc; if (__double_as_longlong(q2) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
     m.reset();
     const double x = MathFast::abs_(a);
     const double r = m.sqrt_(x);
@@ -1320,6 +1275,8 @@ __global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long l
 // mode 4: the portable functions that divide (tan, arctan, arctan2, arcsin, arccos) under MathFast against the same
 // functions under MathIeee, on arguments spread over [-8, 8] (tan, arctan*), [-1, 1] (arcsin, arccos) and tiny values
 __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long seed, unsigned long long* __restrict__ counts) {
+  __shared__ __align__(16) double s_tab[kTabAlloc];
+  const unsigned tab = load_table<256>(s_tab);
   unsigned long long acc = 0, bad = 0;
   auto same = [](double u, double v) { return __double_as_longlong(u) == __double_as_longlong(v); };
   for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
@@ -1327,7 +1284,7 @@ __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long
     const double u0 = (double)(h0 >> 11) * 0x1p-53, u1 = (double)(h1 >> 11) * 0x1p-53;   // [0, 1)
     const double scale = (h0 & 7) == 0 ? 1e-9 : 1.0;
     const double x = (16.0 * u0 - 8.0) * scale, y = (16.0 * u1 - 8.0) * scale, c = (2.0 * u0 - 1.0) * scale;
-    MathFast m;
+    MathFast m(tab);
     double v = p_tan(m, x);
     if (m.ok()) { ++acc; if (!same(v, p_tan(x))) ++bad; }
     m.reset(); v = p_atan(m, x);
@@ -1338,6 +1295,11 @@ __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long
     if (m.ok()) { ++acc; if (!same(v, p_asin(c))) ++bad; }
     m.reset(); v = p_acos(m, c);
     if (m.ok()) { ++acc; if (!same(v, p_acos(c))) ++bad; }
+    // sin / cos do not divide: the two policies differ only in where the coefficient pairs come from
+    ++acc; if (!same(p_sin(m, x), p_sin(x))) ++bad;
+    ++acc; if (!same(p_cos(m, y), p_cos(y))) ++bad;
+    const SinCos qa = sincos_parts(m, x), qb = sincos_parts(x);
+    ++acc; if (!same(qa.s, qb.s) || !same(qa.c, qb.c) || qa.n != qb.n) ++bad;
   }
   if (acc) atomicAdd(counts, acc);
   if (bad) atomicAdd(counts + 1, bad);
@@ -1608,20 +1570,46 @@ int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* 
   return OGG_OK;
 }
 
+// rows per CTA of k_band_fill: among 4..32 the count whose grid fills its last wave best (ties: the smaller tile)
+static i64 band_rows_per_tile(const BandBatch& B, i64 ncb, i64 slots) {
+  static const char* forced = getenv("OGG_BAND_ROWS");   // developer knob (tools/bandbench.py)
+  if (forced && atoi(forced) > 0) return atoi(forced);
+  i64 best_r = 8;
+  double best = -1.0;
+  for (i64 r = 4; r <= 32; ++r) {
+    i64 t = 0;
+    for (int k = 0; k < B.n; ++k) t += (B.b[k].nyp + r - 1) / r;
+    const i64 ctas = t * ncb, waves = (ctas + slots - 1) / slots;
+    // share of the resident slots that do useful rows while the grid runs; a tile's rounding-up of a band's last rows
+    // and the launch's fixed cost per wave both count against large tiles
+    i64 rows = 0;
+    for (int k = 0; k < B.n; ++k) rows += B.b[k].nyp;
+    const double fill = (double)(rows * ncb) / (double)(waves * slots * r);
+    if (fill > best + 1e-9) { best = fill; best_r = r; }
+  }
+  return best_r;
+}
+
 int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, void* stream) {
   if (!bands || nbands < 1 || nbands > kMaxBands) return OGG_ERR_ARG;
   cudaStream_t st = S(stream);
   Scratch ws(st);
   BandBatch B;
-  B.n = nbands; B.Re = Re; B.Re2 = Re * Re; B.total = 0;
-  bool vector_ok = true;
+  B.n = nbands; B.Re = Re; B.Re2 = Re * Re;
+  i64 nxp_max = 0, words = 0;
   for (int k = 0; k < nbands; ++k) {
     const ogg_band_t& a = bands[k];
     if (!a.lam || !a.phi || a.nyp < 1 || a.nxp < 2) return OGG_ERR_ARG;
+    words += 3 * (a.nxp + 2) + 4 * (a.nyp + 2);
+  }
+  double* tables;                                  // one block for every band's seven tables
+  OGG_CUDA(ws.get(&tables, (size_t)words));
+  for (int k = 0; k < nbands; ++k) {
+    const ogg_band_t& a = bands[k];
     const i64 nyp = a.nyp, nxp = a.nxp;
-    double *dxi, *hx, *xd, *cl, *cy, *dyr, *dsl;
-    OGG_CUDA(ws.get(&dxi, nxp)); OGG_CUDA(ws.get(&hx, nxp)); OGG_CUDA(ws.get(&xd, nxp));
-    OGG_CUDA(ws.get(&cl, nyp)); OGG_CUDA(ws.get(&cy, nyp)); OGG_CUDA(ws.get(&dyr, nyp)); OGG_CUDA(ws.get(&dsl, nyp));
+    double *dxi = tables, *hx = dxi + nxp + 2, *xd = hx + nxp + 2, *cl = xd + nxp + 2, *cy = cl + nyp + 2, *dyr = cy + nyp + 2,
+           *dsl = dyr + nyp + 2;
+    tables = dsl + nyp + 2;
     const i64 m = nxp > nyp ? nxp : nyp;
     OGG_LAUNCH(KID_BAND_TABLES, (k_band_tables), (cdiv_u(m, 256), 256), (st), a.lam, a.phi, nyp, nxp, Re, dxi, hx, xd, cl, cy, dyr, dsl);
     OGG_LAUNCH_CHECK();
@@ -1631,25 +1619,23 @@ int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, 
     D.nyp = nyp; D.nxp = nxp;
     D.nyp_v = (a.flags & OGG_BAND_SKIP_TOP_VERTEX_ROW) ? nyp - 1 : nyp;
     D.metrics = (a.flags & OGG_BAND_NO_METRICS) ? 0 : 1;
-    D.v_begin = B.total;
-    B.total += nyp * nxp;
-    // the vector path assumes that the arrays of a family share their alignment modulo 16 bytes
-    auto par = [](const double* q) { return (reinterpret_cast<unsigned long long>(q) >> 3) & 1ull; };
-    const double* famA[4] = {a.x, a.y, a.angle, a.dy};
-    const double* famB[2] = {a.dx, a.area};
-    const double *fa = nullptr, *fb = nullptr;
-    for (const double* q : famA) { if (!q) continue; if (!fa) fa = q; else if (par(q) != par(fa)) vector_ok = false; }
-    for (const double* q : famB) { if (!q) continue; if (!fb) fb = q; else if (par(q) != par(fb)) vector_ok = false; }
+    if (nxp > nxp_max) nxp_max = nxp;
   }
-  // persistent grid: a multiple of the SM count, each CTA an equal share of the flat vertex range (at least a few
-  // hundred vertices per CTA so that tiny bands do not launch idle CTAs)
-  i64 ctas = (i64)num_sms() * 8;
-  const i64 max_useful = (B.total + 511) / 512;
-  if (ctas > max_useful) ctas = max_useful < 1 ? 1 : max_useful;
-  launch_begin(KID_BAND_FILL, st);
-  if (vector_ok) k_band_fill<<<(unsigned)ctas, kBandThreads, 0, st>>>(B);
-  else k_band_fill_scalar<<<(unsigned)ctas, kBandThreads, 0, st>>>(B);
-  launch_end(st);
+  static int occupancy[kMaxDevices] = {0};
+  const int dev = current_device();
+  if (!occupancy[dev]) {
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_band_fill, kBandThreads, 0) != cudaSuccess || occ < 1) occ = 4;
+    occupancy[dev] = occ;
+  }
+  const i64 slots = (i64)num_sms() * occupancy[dev];
+  const i64 ncb = (nxp_max + kBandThreads - 1) / kBandThreads;
+  const i64 R = band_rows_per_tile(B, ncb, slots);
+  B.rows_per_tile = R;
+  i64 tiles = 0;
+  for (int k = 0; k < nbands; ++k) { B.b[k].t_begin = tiles; tiles += (B.b[k].nyp + R - 1) / R; }
+  if (tiles > 65535) return OGG_ERR_ARG;
+  OGG_LAUNCH(KID_BAND_FILL, (k_band_fill), (dim3((unsigned)ncb, (unsigned)tiles), kBandThreads), (st), B);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }

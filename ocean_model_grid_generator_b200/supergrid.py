@@ -315,8 +315,12 @@ class Supergrid(object):
                 jobs.append((piece, c0, c1, off, k == last and self.rank == self.world - 1))
             off += c1 - c0
         if not concurrent or len(jobs) < 2:
+            band_jobs = [j for j in jobs if j[0].kind == "band"]
+            if band_jobs:
+                self._build_bands(band_jobs)
             for job in jobs:
-                self._build_piece(*job)
+                if job[0].kind != "band":
+                    self._build_piece(*job)
                 if host is not None:
                     self._copy_piece_out(host, *job)
             return self
@@ -333,7 +337,7 @@ class Supergrid(object):
         bands = [j for j in jobs if j[0].kind == "band"]
         quads = [] if plan.skip_metrics else [(n % 2, job, "quad") for n, job in enumerate(caps)]
         light_caps = [(2 + n % 2, job, "mesh") for n, job in enumerate(caps)]
-        light_bands = [(4 + n % 2, job, "all") for n, job in enumerate(bands)]
+        light_bands = [(4, bands, "bands")] if bands else []          # every band of the step in ONE persistent launch
         work = (light_bands + quads + light_caps) if host is not None else (quads + light_caps + light_bands)
         used = set()
         for sidx, job, part in work:
@@ -342,10 +346,14 @@ class Supergrid(object):
                 side.wait_event(fork)
                 used.add(sidx)
             with torch.cuda.stream(side):
+                if part == "bands":
+                    self._build_bands(job)
+                    if host is not None:
+                        for bjob in job:
+                            self._copy_piece_out(host, *bjob)
+                    continue
                 self._build_piece(*job, part=part)
-                if host is not None and part == "all":
-                    self._copy_piece_out(host, *job)
-                elif host is not None and part == "mesh":
+                if host is not None and part == "mesh":
                     for qidx, qjob, _ in quads:
                         if qjob is job:
                             events[7].record(streams[qidx])
@@ -373,6 +381,28 @@ class Supergrid(object):
         return (_dev.ptr_off(self.x, off * nxp), _dev.ptr_off(self.y, off * nxp), _dev.ptr_off(self.dx, off * (nxp - 1)),
                 _dev.ptr_off(self.dy, off * nxp), _dev.ptr_off(self.area, off * (nxp - 1)),
                 _dev.ptr_off(self.angle_dx, off * nxp), st)
+
+    def _band_desc(self, piece, c0, c1, off, closing):
+        plan, nxp = self.plan, self.plan.nxp
+        px, py, pdx, pdy, parea, pangle, _ = self._views(off, c1 - c0 + 1)
+        key = id(piece)
+        if key not in self._lam_dev:
+            self._lam_dev[key] = (_dev.to_dev(piece.p["lam"]), _dev.to_dev(piece.p["phi"]))
+        lam, phi = self._lam_dev[key]
+        flags = 0 if closing else _cabi.OGG_BAND_SKIP_TOP_VERTEX_ROW
+        if plan.skip_metrics:
+            flags |= _cabi.OGG_BAND_NO_METRICS
+            pdx = pdy = parea = None
+        v = lambda q: q.value if q is not None else None            # noqa: E731
+        return _cabi.OggBand(v(_dev.ptr(lam)), v(_dev.ptr_off(phi, piece.row0 + c0)), c1 - c0 + 1, nxp, flags,
+                             v(px), v(py), v(pdx), v(pdy), v(parea), v(pangle))
+
+    def _build_bands(self, jobs):
+        """All band pieces of this rank's share in one launch of the persistent fill kernel (ogg_band_fill_metrics_batch)."""
+        for k in range(0, len(jobs), 4):
+            group = jobs[k:k + 4]
+            arr = (_cabi.OggBand * len(group))(*[self._band_desc(*job) for job in group])
+            _cabi.call("ogg_band_fill_metrics_batch", arr, len(group), Re, _dev.stream())
 
     def _build_piece(self, piece, c0, c1, off, closing, part="all"):
         """part: "all", or for a cap "mesh" (x, y, angle_dx) / "quad" (dx, dy, area) -- independent outputs."""
