@@ -278,12 +278,13 @@ struct BandBatch { BandDesc b[kMaxBands]; int n; i64 rows_per_tile; double Re, R
 
 OGG_DI double band_angle(double xdv, double cyj, double dyc, double ang_pos, double ang_neg) {
   // angle_x on a band (:725-728): y[ia]-y[ib] = phi-phi = +0, so p_atan2 takes its ay == 0 branch: +0 for a
-  // non-negative second argument, pi - (0 - pi_lo) for a negative one -- two constants; anything else (NaN) goes
-  // through the general code.
+  // non-negative second argument, pi - (0 - pi_lo) for a negative one -- two constants.  What is left is a NaN first
+  // argument (phi not finite) or a NaN second one: the spec's arctan2 returns NaN for both (its quotient is NaN and no
+  // range test of arctan takes a NaN), which is what the sum below is -- without the general code's 90 registers.
   const double arg = xdv * cyj;
   if (dyc == 0.0 && arg >= 0.0) return ang_pos;
   if (dyc == 0.0 && arg < 0.0) return ang_neg;
-  return p_atan2(dyc, arg) / kPi180;
+  return dyc + arg;
 }
 OGG_DI double band_dx(double dxiv, double clj, double dyc, double Re) {
   // dx (:698): dy_i = +0 and sqrt(0 + tt*tt) = |tt|: sqrt(fl(t*t)) == |t| in binary floating point, round-to-nearest,
@@ -295,48 +296,51 @@ OGG_DI double band_dx(double dxiv, double clj, double dyc, double Re) {
   const double root = (dy_i == 0.0 && t2 >= 0x1p-1000 && t2 <= 0x1p1000) ? fabs(tt) : sqrt(dy_i * dy_i + t2);
   return Re * root;
 }
-constexpr int kBandThreads = 256;
-__global__ void __launch_bounds__(kBandThreads) k_band_fill(const __grid_constant__ BandBatch B) {
-  int k = 0;
-  while (k + 1 < B.n && (i64)blockIdx.y >= B.b[k + 1].t_begin) ++k;
-  const double* __restrict__ lam = B.b[k].lam;
-  const double* __restrict__ phi = B.b[k].phi;
-  const double* __restrict__ cl = B.b[k].cl;
-  const double* __restrict__ cy = B.b[k].cy;
-  const double* __restrict__ dyr = B.b[k].dyr;
-  const double* __restrict__ dsl = B.b[k].dsl;
-  double* __restrict__ x = B.b[k].x;
-  double* __restrict__ y = B.b[k].y;
-  double* __restrict__ dx = B.b[k].dx;
-  double* __restrict__ dy = B.b[k].dy;
-  double* __restrict__ area = B.b[k].area;
-  double* __restrict__ angle = B.b[k].angle;
-  const i64 nxp = B.b[k].nxp, nx = nxp - 1, nyp = B.b[k].nyp, nyp_v = B.b[k].nyp_v;
-  const int metrics = B.b[k].metrics;
+#ifndef OGG_BAND_THREADS
+#define OGG_BAND_THREADS 256
+#endif
+constexpr int kBandThreads = OGG_BAND_THREADS;
+#ifndef OGG_BAND_ROWS
+#define OGG_BAND_ROWS 8
+#endif
+#ifndef OGG_BAND_MINB
+#define OGG_BAND_MINB 5
+#endif
+constexpr int kBandRows = OGG_BAND_ROWS;
+// kBandRows rows of one band from row j0 on, one column per thread.  D is a statically indexed member of the kernel
+// parameter, so its pointers and sizes are constant-bank operands (a dynamically indexed descriptor costs ~50 registers).
+OGG_DI void band_rows(const BandDesc& D, i64 j0, double Re, double Re2) {
+  const i64 nxp = D.nxp, nx = nxp - 1, nyp = D.nyp;
   const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   if (i >= nxp) return;
   const bool cell = i < nx;
-  const double lamv = lam[i], xdv = B.b[k].xd[i];
-  const double dxiv = cell ? B.b[k].dxi[i] : 0.0, hxv = cell ? B.b[k].hx[i] : 0.0;
-  const i64 j0 = ((i64)blockIdx.y - B.b[k].t_begin) * B.rows_per_tile;
-  const i64 j1 = j0 + B.rows_per_tile < nyp ? j0 + B.rows_per_tile : nyp;
+  const double lamv = D.lam[i], xdv = D.xd[i];
+  const double dxiv = cell ? D.dxi[i] : 0.0, hxv = cell ? D.hx[i] : 0.0;
   const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
-  const double Re = B.Re, Re2 = B.Re2;
-#pragma unroll 4
-  for (i64 j = j0; j < j1; ++j) {
-    const double phij = phi[j];
+#pragma unroll
+  for (int r = 0; r < kBandRows; ++r) {
+    const i64 j = j0 + r;
+    if (j >= nyp) break;
+    const double phij = D.phi[j];
     const double dyc = phij - phij;  // y[ia]-y[ib] on a band: +0 unless phi is not finite
-    if (j < nyp_v) {
-      if (x) x[j * nxp + i] = lamv;
-      if (y) y[j * nxp + i] = phij;
-      if (angle) angle[j * nxp + i] = band_angle(xdv, cy[j], dyc, ang_pos, ang_neg);
-      if (metrics && cell && dx) dx[j * nx + i] = band_dx(dxiv, cl[j], dyc, Re);
+    if (j < D.nyp_v) {
+      if (D.x) D.x[j * nxp + i] = lamv;
+      if (D.y) D.y[j * nxp + i] = phij;
+      if (D.angle) D.angle[j * nxp + i] = band_angle(xdv, D.cy[j], dyc, ang_pos, ang_neg);
+      if (D.metrics && cell && D.dx) D.dx[j * nx + i] = band_dx(dxiv, D.cl[j], dyc, Re);
     }
-    if (metrics && j < nyp - 1) {
-      if (dy) dy[j * nxp + i] = dyr[j];
-      if (cell && area) area[j * nx + i] = Re2 * (hxv * dsl[j]);
+    if (D.metrics && j < nyp - 1) {
+      if (D.dy) D.dy[j * nxp + i] = D.dyr[j];
+      if (cell && D.area) D.area[j * nx + i] = Re2 * (hxv * D.dsl[j]);
     }
   }
+}
+__global__ void __launch_bounds__(kBandThreads, OGG_BAND_MINB) k_band_fill(const __grid_constant__ BandBatch B) {
+  const i64 t = blockIdx.y;
+  if (B.n > 3 && t >= B.b[3].t_begin) band_rows(B.b[3], (t - B.b[3].t_begin) * kBandRows, B.Re, B.Re2);
+  else if (B.n > 2 && t >= B.b[2].t_begin) band_rows(B.b[2], (t - B.b[2].t_begin) * kBandRows, B.Re, B.Re2);
+  else if (B.n > 1 && t >= B.b[1].t_begin) band_rows(B.b[1], (t - B.b[1].t_begin) * kBandRows, B.Re, B.Re2);
+  else band_rows(B.b[0], t * kBandRows, B.Re, B.Re2);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1570,26 +1574,6 @@ int ogg_arctan2(const double* y, const double* x, double* out, int64_t n, void* 
   return OGG_OK;
 }
 
-// rows per CTA of k_band_fill: among 4..32 the count whose grid fills its last wave best (ties: the smaller tile)
-static i64 band_rows_per_tile(const BandBatch& B, i64 ncb, i64 slots) {
-  static const char* forced = getenv("OGG_BAND_ROWS");   // developer knob (tools/bandbench.py)
-  if (forced && atoi(forced) > 0) return atoi(forced);
-  i64 best_r = 8;
-  double best = -1.0;
-  for (i64 r = 4; r <= 32; ++r) {
-    i64 t = 0;
-    for (int k = 0; k < B.n; ++k) t += (B.b[k].nyp + r - 1) / r;
-    const i64 ctas = t * ncb, waves = (ctas + slots - 1) / slots;
-    // share of the resident slots that do useful rows while the grid runs; a tile's rounding-up of a band's last rows
-    // and the launch's fixed cost per wave both count against large tiles
-    i64 rows = 0;
-    for (int k = 0; k < B.n; ++k) rows += B.b[k].nyp;
-    const double fill = (double)(rows * ncb) / (double)(waves * slots * r);
-    if (fill > best + 1e-9) { best = fill; best_r = r; }
-  }
-  return best_r;
-}
-
 int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, void* stream) {
   if (!bands || nbands < 1 || nbands > kMaxBands) return OGG_ERR_ARG;
   cudaStream_t st = S(stream);
@@ -1621,16 +1605,8 @@ int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, 
     D.metrics = (a.flags & OGG_BAND_NO_METRICS) ? 0 : 1;
     if (nxp > nxp_max) nxp_max = nxp;
   }
-  static int occupancy[kMaxDevices] = {0};
-  const int dev = current_device();
-  if (!occupancy[dev]) {
-    int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_band_fill, kBandThreads, 0) != cudaSuccess || occ < 1) occ = 4;
-    occupancy[dev] = occ;
-  }
-  const i64 slots = (i64)num_sms() * occupancy[dev];
   const i64 ncb = (nxp_max + kBandThreads - 1) / kBandThreads;
-  const i64 R = band_rows_per_tile(B, ncb, slots);
+  const i64 R = kBandRows;
   B.rows_per_tile = R;
   i64 tiles = 0;
   for (int k = 0; k < nbands; ++k) { B.b[k].t_begin = tiles; tiles += (B.b[k].nyp + R - 1) / R; }

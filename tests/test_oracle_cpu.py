@@ -359,3 +359,28 @@ def test_oracle_slab_composition_equals_whole(oracle):
     rows = {whole["area"][j].tobytes() for j in range(whole["area"].shape[0])}
     for p in parts:
         assert all(p["area"][j].tobytes() in rows for j in range(p["area"].shape[0]))
+
+
+def test_opcount_json_is_what_the_oracle_derives():
+    """bench.py's roofline numerators come from profiles/opcount.json; that file must be what tools/opcount.py derives
+    from the oracle (operator-counting scalar, oracle/opcount.cpp), not typed in.  Re-derived here at r=1 (the per-unit
+    counts depend on the resolution only through the share of samples on special rows/columns: < 0.1 %)."""
+    import json
+    import shutil
+    import sys
+    if shutil.which("g++") is None:
+        pytest.skip("g++ not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    import opcount
+    d = opcount.derive(1.0)
+    ref = json.load(open(os.path.join(root, "profiles", "opcount.json")))
+    for unit in ("bipolar_sample", "dp_vertex", "haversine", "dp_hsample"):
+        for w in ("ops_8d", "ops_issue", "ops_reference"):
+            a, b = d["totals"][unit][w], ref["totals"][unit][w]
+            assert abs(a - b) <= 0.005 * b, (unit, w, a, b)
+    # the composite is its parts: 4*NV projections + 2*NV great-arc distances + the finite-difference combination
+    t = ref["totals"]
+    nv = 2
+    comp = 4 * nv * t["dp_vertex"]["ops_8d"] + 2 * nv * t["haversine"]["ops_8d"] + t["fd_combine_x2"]["ops_8d"]
+    assert abs(comp - t["dp_hsample"]["ops_8d"]) <= 0.01 * comp, (comp, t["dp_hsample"]["ops_8d"])
