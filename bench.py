@@ -611,7 +611,11 @@ def run_ours(args):
         ach = BYTES_BAND_VERTEX * units["band_fill"] / (per_step_ms * 1e-3) / 1e9
         roof_hbm = {"kernel": "band_fill", "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                     "frac": ach / hbm_peak, "peak_source": hbm_src, "kernel_ms_per_step": per_step_ms,
-                    "traffic": (ncu.get("kernels", {}).get("band_fill") or {}).get("dram_bytes_per_launch_all_band_launches"),
+                    "traffic": ((ncu.get("kernels", {}).get("band_fill") or {}).get("dram_bytes_per_launch")
+                                if r == 4 and world == 1 and not args.slabs else None),
+                    "traffic_note": "DRAM bytes of the one launch that fills both bands, from the committed ncu capture; below the "
+                                    "algorithmic bytes because part of the last rows is still in the 126 MB L2 when the kernel ends",
+                    "algorithmic_bytes_per_step": BYTES_BAND_VERTEX * units["band_fill"],
                     "measured_in": "single-stream pass (in the timed region the band fills overlap the cap kernels)"}
     if roof is None:
         roof = roof_hbm
