@@ -492,7 +492,9 @@ def run_ours(args):
                 s2 = SG.Supergrid(p2, rank, world)
             t1 = time.perf_counter()
             if pinned is None:
-                pinned = s2.pinned_like()
+                with D.host_near_device() as near:      # host pages on the GPU's own NUMA node (matters on 2-socket boxes)
+                    pinned = s2.pinned_like()
+                numa_bound = near.bound
             s2.build(host=pinned)        # every piece's rows are copied out on its own stream while the caps compute
             # the step's results read on the host: the six arrays (above) and the global-area check (device tree sum,
             # 8 bytes).  No host-side parallel reduction here: an OpenMP pool left spinning after torch's CPU sum
@@ -514,7 +516,7 @@ def run_ours(args):
         e2e = {"value": npoints / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms": float(te[0]) * 1e3, "statistic": "median of 5 timed iterations (max over ranks), after one untimed",
                "plan_ms": float(te[1]) * 1e3, "d2h_gbs_this_rank": d2h / max(1e-9, float(te[0]) - float(te[1])) / 1e9,
-               "checksum_area_local": checksum, "host_area_last_cell": corner}
+               "checksum_area_local": checksum, "host_area_last_cell": corner, "pinned_on_gpu_numa_node": numa_bound}
         del pinned
 
     # ---- N > 1: the halo path on the wire; every N: the fixed-size (strong-scaling) runs of configs[2..4] -------------

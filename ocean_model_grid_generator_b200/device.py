@@ -61,3 +61,54 @@ def ptr_off(t, elem_offset):
 
 def stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def bind_host_to_device(index=None):
+    """Binds the calling thread to the CPUs next to CUDA device `index` (default: the current device), so that pinned host
+    buffers allocated afterwards (first touch) and the copy/submit threads sit on the GPU's own NUMA node.  On a
+    two-socket 8-GPU box a rank whose pinned buffer lives on the other socket copies device->host across the socket
+    link.  Returns the CPU list it bound to, or None when NVML / the topology is not available (nothing changes then).
+    Call it once per rank before allocating pinned memory (bench.py and the CLI do when OGG_NUMA_BIND != 0)."""
+    import os
+    try:
+        import pynvml
+        if index is None:
+            index = torch.cuda.current_device()
+        pynvml.nvmlInit()
+        # NVML enumerates in PCI order; map through the bus id torch reports so that CUDA_VISIBLE_DEVICES is honoured
+        props = torch.cuda.get_device_properties(index)
+        bus = "%08x:%02x:%02x.0" % (getattr(props, "pci_domain_id", 0), props.pci_bus_id, props.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w in range(words) for b in range(64) if (int(mask[w]) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
+class host_near_device:
+    """`with host_near_device(): buf = pinned allocation` -- runs the body bound to the CPUs of the current device's NUMA
+    node (see bind_host_to_device) and restores the thread's affinity afterwards, so that only the placement of the host
+    pages changes.  `.bound` tells whether the topology was available.  OGG_NUMA_BIND=0 turns it off."""
+
+    def __init__(self, index=None):
+        self.index, self.bound, self._saved = index, False, None
+
+    def __enter__(self):
+        import os
+        if os.environ.get("OGG_NUMA_BIND", "1") != "0":
+            self._saved = os.sched_getaffinity(0)
+            self.bound = bind_host_to_device(self.index) is not None
+        return self
+
+    def __exit__(self, *exc):
+        import os
+        if self._saved is not None:
+            os.sched_setaffinity(0, self._saved)
+        return False
