@@ -692,8 +692,10 @@ OGG_DI double sample_index_at(const QuadNodes& q, int n, i64 c0, i64 c1, i64 tot
 // (+ the exact pole row when j1 == ny): one launch replaces k_sample_index x2 + k_bp_tables x2.
 __global__ void __launch_bounds__(256) k_bp_quad_tables(QuadNodes q, int n, i64 nx, i64 ny, i64 j0, i64 j1, i64 nuc,
                                                         i64 nur, double lat0_bp, double lon_bp, double rp,
-                                                        BpCol* __restrict__ ct, BpRow* __restrict__ rt) {
+                                                        BpCol* __restrict__ ct, BpRow* __restrict__ rt,
+                                                        double* __restrict__ divs) {
   const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
+  if (t < 3) MathFast::store_divisor(divs + 2 * t, t == 0 ? kPi180 : (t == 1 ? (double)nx : (double)ny));   // see MathFast::Divisor
   if (t < nuc) {
     const double idx = sample_index_at(q, n, 0, nx, nx, 0, t);
     ct[t] = bp_col(lon_bp + (idx * 360.0) / (double)nx, lon_bp);                 // :126
@@ -721,8 +723,13 @@ __device__ __noinline__ HiHj bp_qsample_ieee(BpRow R, BpCol C, double lon_bp, do
   return HiHj{((a * 2) * kPi) / dnx,                                              // :131
               ((b * (90 - lat0_bp)) * kPi180) / dny};                             // :132
 }
+#ifndef OGG_BP_THREADS
+#define OGG_BP_THREADS 256
+#endif
+constexpr int kBpThreads = OGG_BP_THREADS;
 template <int N, int TR, int TC>
-__global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt, i64 nuc,
+__global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt,
+                                                       const double* __restrict__ divs, i64 nuc,
                                                        i64 ncr, i64 nx, i64 ny, double lat0_bp, double lon_bp, double rp,
                                                        double Re, double* __restrict__ dxq, double* __restrict__ dyq,
                                                        double* __restrict__ daq) {
@@ -730,10 +737,11 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
   extern __shared__ double smem[];
   double* sx = smem;
   double* sy = smem + SR * SCP;
-  __shared__ __align__(16) double s_tab[kTabAlloc];
   const i64 gr0 = (i64)blockIdx.y * TR * (N - 1), gc0 = (i64)blockIdx.x * TC * (N - 1);
   const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
-  MathFast mf(load_table<256>(s_tab, (double)nx, (double)ny));   // cached divisors: pi/180, nx, ny (all moderate: nx, ny >= 1)
+  // cached divisors pi/180, nx, ny (all moderate: nx, ny >= 1) with their refined reciprocals, stored by k_bp_quad_tables
+  MathFast mf(divs);
+  const MathFast::Divisor dnx = MathFast::load_divisor(divs + 2), dny = MathFast::load_divisor(divs + 4);
   // one sample: scaled h_i_inv, h_j_inv of unique row r / column c of this tile -> shared memory
   auto sample = [&](int r, int c, const BpCol& C, bool col_ok) {
     const i64 gr = gr0 + r;
@@ -743,8 +751,8 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
       double l, p;
       mf.reset();
       bp_sample<false>(mf, R, C, lon_bp, rp, l, p, a, b);
-      a = mf.div_slot<1>((a * 2) * kPi);                                          // :131
-      b = mf.div_slot<2>((b * (90 - lat0_bp)) * kPi180);                          // :132
+      a = mf.div_by((a * 2) * kPi, dnx);                                         // :131
+      b = mf.div_by((b * (90 - lat0_bp)) * kPi180, dny);                         // :132
       if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, the lon_bp meridian)
         const HiHj o = bp_qsample_ieee(R, C, lon_bp, rp, lat0_bp, (double)nx, (double)ny);
         a = o.a; b = o.b;
@@ -757,7 +765,8 @@ __global__ void __launch_bounds__(256, OGG_BP_MINB) k_bp_quad_fused(const BpCol*
   // a thread keeps ONE sample column (its column-table entry stays in registers, a warp covers 32 consecutive
   // columns of one row, whose row-table entry is a broadcast load) and walks down the rows, G row-interleaved groups
   // of SC-1 threads; the tile's last column goes to the first SR threads of the last group, which has the fewest rows.
-  constexpr int CM = SC - 1, G = 256 / CM;
+  constexpr int CM = SC - 1, G = kBpThreads / CM;
+  static_assert(G >= 1 && SR <= CM, "a row of sample columns per thread group");
   const int grp = threadIdx.x / CM, cm = threadIdx.x - grp * CM;
   if (grp < G) {
     const bool col_ok = gc0 + cm < nuc;
@@ -1047,8 +1056,8 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
 __device__ __noinline__ double haversine_ieee(double lam0, double phi0, double lam1, double phi1) {
   return haversine(lam0, phi0, lam1, phi1);
 }
-__device__ __noinline__ double haversine_ol(unsigned tab, double lam0, double phi0, double lam1, double phi1) {
-  MathFast m(tab);
+__device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
+  MathFast m;
   const double v = haversine(m, lam0, phi0, lam1, phi1);
   return m.ok() ? v : haversine_ieee(lam0, phi0, lam1, phi1);   // e.g. coincident points: sqrt(0), asin(0)
 }
@@ -1099,9 +1108,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
   __shared__ double phiS[NM][THREADS];
   __shared__ unsigned shw[2 * kWarps];
   __shared__ unsigned s_state;
-  __shared__ __align__(16) double s_tab[kTabAlloc];
   const DpConst K = dp_load(cst);
-  MathFast mf(load_table<THREADS>(s_tab));
+  MathFast mf(cst + 3);                                  // pi/180 and its refined reciprocal, stored by k_dp_quad_setup
   const i64 ntile = (ncol + TW - 1) / TW;
   const i64 nitem = nrow * ntile;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -1187,7 +1195,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         double l0 = lamS[2 * q][threadIdx.x], l1 = lamS[2 * q + 1][threadIdx.x];
         if ((st >> (2 * q)) & 1u) l0 = l0 - 360;                           // :473
         if ((st >> (2 * q + 1)) & 1u) l1 = l1 - 360;
-        phiS[2 * q][threadIdx.x] = haversine_ol(mf.tab, l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
+        phiS[2 * q][threadIdx.x] = haversine_ol(l0, phiS[2 * q][threadIdx.x], l1, phiS[2 * q + 1][threadIdx.x]);
       }
       // pair 2m = i-direction at level m, pair 2m+1 = j-direction (:538-546, :553-561)
       hx[r * ncol + c] = fd_combine<2 * NV>(phiS[0][threadIdx.x], NV > 1 ? phiS[4][threadIdx.x] : 0.0,
@@ -1247,22 +1255,22 @@ OGG_DI double gen_operand(unsigned long long h, int mode) {
 // from the IEEE result; counts[2]: sets in MathFast's documented range that a guard rejected (must be 0 for modes != 1)
 __global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long long seed, int mode,
                                                           unsigned long long* __restrict__ counts) {
-  __shared__ __align__(16) double s_tab[kTabAlloc];
-  const unsigned tab = load_table<256>(s_tab);
   unsigned long long acc = 0, bad = 0, rej = 0;
   for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
     const unsigned long long h0 = splitmix64(seed + 2ull * (unsigned long long)e), h1 = splitmix64(h0 ^ 0x5851f42d4c957f2dull);
     const double a = gen_operand(h0, mode), b = gen_operand(h1, mode);
-    MathFast m(tab);
+    MathFast m;
     const double q = m.div(a, b);
     if (m.ok()) { ++acc; if (__double_as_longlong(q) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
     m.reset();
     const double q1 = m.div_num_ok(1.0, b);
     if (m.ok()) { ++acc; if (__double_as_longlong(q1) != __double_as_longlong(1.0 / b)) ++bad; } else if (mode != 1) ++rej;
     m.reset();
-    const MathFast::Divisor d = m.divisor(b);
+    double by[2];
+    MathFast::store_divisor(by, b);                       // what a set-up kernel stores ...
+    const MathFast::Divisor d = MathFast::load_divisor(by);   // ... and a quadrature kernel loads
     const double q2 = m.div_by(a, d);
-    if (m.ok() && d.valid) { ++acc; if (__double_as_longlong(q2) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
+    if (m.ok() && d.y == d.y) { ++acc; if (__double_as_longlong(q2) != __double_as_longlong(a / b)) ++bad; } else if (mode != 1) ++rej;
     m.reset();
     const double x = MathFast::abs_(a);
     const double r = m.sqrt_(x);
@@ -1279,8 +1287,6 @@ __global__ void __launch_bounds__(256) k_selftest_divsqrt(i64 n, unsigned long l
 // mode 4: the portable functions that divide (tan, arctan, arctan2, arcsin, arccos) under MathFast against the same
 // functions under MathIeee, on arguments spread over [-8, 8] (tan, arctan*), [-1, 1] (arcsin, arccos) and tiny values
 __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long seed, unsigned long long* __restrict__ counts) {
-  __shared__ __align__(16) double s_tab[kTabAlloc];
-  const unsigned tab = load_table<256>(s_tab);
   unsigned long long acc = 0, bad = 0;
   auto same = [](double u, double v) { return __double_as_longlong(u) == __double_as_longlong(v); };
   for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < n; e += (i64)gridDim.x * blockDim.x) {
@@ -1288,7 +1294,7 @@ __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long
     const double u0 = (double)(h0 >> 11) * 0x1p-53, u1 = (double)(h1 >> 11) * 0x1p-53;   // [0, 1)
     const double scale = (h0 & 7) == 0 ? 1e-9 : 1.0;
     const double x = (16.0 * u0 - 8.0) * scale, y = (16.0 * u1 - 8.0) * scale, c = (2.0 * u0 - 1.0) * scale;
-    MathFast m(tab);
+    MathFast m;
     double v = p_tan(m, x);
     if (m.ok()) { ++acc; if (!same(v, p_tan(x))) ++bad; }
     m.reset(); v = p_atan(m, x);
@@ -1424,13 +1430,16 @@ static int run_quad_cells(int order, const double* sx, const double* sy, i64 nuc
 #ifndef OGG_BP_TR
 #define OGG_BP_TR 6
 #endif
-constexpr int kBpTileRows = OGG_BP_TR, kBpTileCols = 32;  // 53 KB of samples per CTA: 4 CTAs/SM (8x32: 3 CTAs/SM, 3.6 % slower)
+#ifndef OGG_BP_TC
+#define OGG_BP_TC 32
+#endif
+constexpr int kBpTileRows = OGG_BP_TR, kBpTileCols = OGG_BP_TC;  // 53 KB of samples per CTA: 4 CTAs/SM (8x32: 3 CTAs/SM, 3.6 % slower)
 template <int N>
-static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
+static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, const double* divs, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
                                 double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq,
                                 cudaStream_t st) {
   constexpr int TR = kBpTileRows, TC = kBpTileCols;
-  static_assert(TR * TC <= 256, "one thread per cell");
+  static_assert(TR * TC <= kBpThreads, "one thread per cell");
   constexpr size_t smem = sizeof(double) * 2 * ((N - 1) * TR + 1) * ((N - 1) * (TC + 1));
   static bool configured[kMaxDevices] = {false};   // the opt-in to > 48 KB of dynamic shared memory is per device
   const int dev = current_device();
@@ -1440,17 +1449,17 @@ static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, i64 nuc, i64 n
   }
   const dim3 g(cdiv_u(nx, TC), cdiv_u(ncr, TR));
   launch_begin(KID_BP_QUAD, st);
-  k_bp_quad_fused<N, TR, TC><<<g, 256, smem, st>>>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq);
+  k_bp_quad_fused<N, TR, TC><<<g, kBpThreads, smem, st>>>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq);
   launch_end(st);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
-static int run_bp_quad_fused(int order, const BpCol* ct, const BpRow* rt, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
+static int run_bp_quad_fused(int order, const BpCol* ct, const BpRow* rt, const double* divs, i64 nuc, i64 ncr, i64 nx, i64 ny, double lat0_bp,
                              double lon_bp, double rp, double Re, double* dxq, double* dyq, double* daq, cudaStream_t st) {
-  if (order == 2) return launch_bp_quad_fused<2>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
-  if (order == 3) return launch_bp_quad_fused<3>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
-  if (order == 4) return launch_bp_quad_fused<4>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
-  return launch_bp_quad_fused<5>(ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (order == 2) return launch_bp_quad_fused<2>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (order == 3) return launch_bp_quad_fused<3>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  if (order == 4) return launch_bp_quad_fused<4>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  return launch_bp_quad_fused<5>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
 }
 
 // cap on the per-chunk sample scratch of the quadrature drivers (bytes of dx+dy samples)
@@ -1712,12 +1721,12 @@ int ogg_bipolar_cap_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, 
   const i64 nuc = (order - 1) * nx + 1;
   const i64 nur = (order - 1) * ncr + 1 + (top ? 1 : 0);  // + the exact pole row
   Scratch ws(st);
-  BpCol* ct; BpRow* rt;
-  OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, nur));
+  BpCol* ct; BpRow* rt; double* divs;
+  OGG_CUDA(ws.get(&ct, nuc)); OGG_CUDA(ws.get(&rt, nur)); OGG_CUDA(ws.get(&divs, 6));
   const i64 m = nuc > nur ? nuc : nur;
-  OGG_LAUNCH(KID_BP_TABLES, (k_bp_quad_tables), (cdiv_u(m, 256), 256), (st), q, order, nx, ny, j0, j1, nuc, nur, lat0_bp, lon_bp, rp, ct, rt);
+  OGG_LAUNCH(KID_BP_TABLES, (k_bp_quad_tables), (cdiv_u(m, 256), 256), (st), q, order, nx, ny, j0, j1, nuc, nur, lat0_bp, lon_bp, rp, ct, rt, divs);
   OGG_LAUNCH_CHECK();
-  int rc = run_bp_quad_fused(order, ct, rt, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
+  int rc = run_bp_quad_fused(order, ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq, st);
   if (rc) return rc;
   if (top) {
     const dim3 g(cdiv_u(nx, 128)), b(128);
@@ -1869,7 +1878,10 @@ __global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i
   DpConst K;
   K.r_joint = p_tan((90 + lat0) * kPi180);                                                 // :494
   K.z0 = cmul(Cx{r_pole, 0.0}, cis_np(lam_pole * kPi180));                                 // :495
-  if (t == 0) { cst[0] = K.r_joint; cst[1] = K.z0.re; cst[2] = K.z0.im; }
+  if (t == 0) {
+    cst[0] = K.r_joint; cst[1] = K.z0.re; cst[2] = K.z0.im;
+    MathFast::store_divisor(cst + 3, kPi180);                                              // see MathFast::Divisor
+  }
   const int nt = 1 + 2 * nv;
   const i64 nuc = (order - 1) * nx + 1, nur = (order - 1) * (c1 - c0) + 1;
   const bool col = do_cols && t < nuc, row = t < nur;
@@ -1988,7 +2000,7 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
   Cx* ct;
   unsigned long long* desc;
   const i64 max_items = dp_hsamples_items(nv, max_nur, nuc);
-  OGG_CUDA(ws.get(&cst, 3));
+  OGG_CUDA(ws.get(&cst, 5));
   OGG_CUDA(ws.get(&ct, nuc * nt)); OGG_CUDA(ws.get(&rt, max_nur * nt)); OGG_CUDA(ws.get(&x0v, 12));
   OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
   OGG_CUDA(ws.get(&desc, (size_t)max_items + 1));
