@@ -317,6 +317,9 @@ OGG_DI void band_rows(const BandDesc& D, i64 j0, double Re, double Re2) {
   const double lamv = D.lam[i], xdv = D.xd[i];
   const double dxiv = cell ? D.dxi[i] : 0.0, hxv = cell ? D.hx[i] : 0.0;
   const double ang_pos = 0.0 / kPi180, ang_neg = (kPi - (0.0 - kC[kPiLo])) / kPi180;
+  // dy (:699-700) has x[j+1,i]-x[j,i] = lam-lam under its root: +0 for a finite longitude (then dy is the row table's
+  // value), NaN for a NaN or infinite one (then dy is NaN)
+  const double dxc = lamv - lamv;
 #pragma unroll
   for (int r = 0; r < kBandRows; ++r) {
     const i64 j = j0 + r;
@@ -330,7 +333,7 @@ OGG_DI void band_rows(const BandDesc& D, i64 j0, double Re, double Re2) {
       if (D.metrics && cell && D.dx) D.dx[j * nx + i] = band_dx(dxiv, D.cl[j], dyc, Re);
     }
     if (D.metrics && j < nyp - 1) {
-      if (D.dy) D.dy[j * nxp + i] = D.dyr[j];
+      if (D.dy) D.dy[j * nxp + i] = dxc == 0.0 ? D.dyr[j] : dxc;
       if (cell && D.area) D.area[j * nx + i] = Re2 * (hxv * D.dsl[j]);
     }
   }

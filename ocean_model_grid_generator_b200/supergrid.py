@@ -398,7 +398,7 @@ class Supergrid(object):
                              v(px), v(py), v(pdx), v(pdy), v(parea), v(pangle))
 
     def _build_bands(self, jobs):
-        """All band pieces of this rank's share in one launch of the persistent fill kernel (ogg_band_fill_metrics_batch)."""
+        """All band pieces of this rank's share in one launch of the fill kernel (ogg_band_fill_metrics_batch)."""
         for k in range(0, len(jobs), 4):
             group = jobs[k:k + 4]
             arr = (_cabi.OggBand * len(group))(*[self._band_desc(*job) for job in group])

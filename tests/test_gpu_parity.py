@@ -294,6 +294,64 @@ def test_band_fused_equals_general(G, oracle):
     assert_bits(D.to_host(o[5]), oracle.angle_x(x, y), "angle")
 
 
+def _band_outputs(D, nyp, nxp):
+    return [D.empty(nyp, nxp), D.empty(nyp, nxp), D.empty(nyp, nxp - 1), D.empty(nyp - 1, nxp), D.empty(nyp - 1, nxp - 1), D.empty(nyp, nxp)]
+
+
+def test_band_batch_equals_single_calls(G):
+    """ogg_band_fill_metrics_batch (every band of a stitch in ONE launch) against one ogg_band_fill_metrics call per band:
+    four bands of different shapes (ragged last row tile, a 2-column band, odd/even row lengths), with the
+    SKIP_TOP_VERTEX_ROW and NO_METRICS flags, output buffers pre-filled with a sentinel so that a row the flags
+    exclude must come back untouched."""
+    import ctypes
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    rng = np.random.default_rng(11)
+    shapes = [(37, 721), (9, 2), (130, 1442), (1, 300)]
+    flags = [0, 1, 2, 0]          # OGG_BAND_SKIP_TOP_VERTEX_ROW = 1, OGG_BAND_NO_METRICS = 2 (include/ogg_b200.h)
+    bands = (_cabi.OggBand * len(shapes))()
+    keep, single = [], []
+    for k, ((nyp, nxp), fl) in enumerate(zip(shapes, flags)):
+        lam = D.to_dev(-300.0 + np.sort(rng.uniform(0, 360, nxp)))
+        phi = D.to_dev(np.sort(rng.uniform(-80, 80, nyp)))
+        a, b = _band_outputs(D, nyp, nxp), _band_outputs(D, nyp, nxp)
+        for t in a + b:
+            t.fill_(-777.0)
+        _cabi.call("ogg_band_fill_metrics", D.ptr(lam), D.ptr(phi), nyp, nxp, 6371.0e3, fl, *[D.ptr(t) for t in a], D.stream())
+        bd = bands[k]
+        bd.lam, bd.phi, bd.nyp, bd.nxp, bd.flags = D.ptr(lam).value, D.ptr(phi).value, nyp, nxp, fl
+        bd.x, bd.y, bd.dx, bd.dy, bd.area, bd.angle = [D.ptr(t).value for t in b]
+        keep.append((lam, phi)); single.append((a, b))
+    _cabi.call("ogg_band_fill_metrics_batch", bands, len(shapes), 6371.0e3, D.stream())
+    for k, (a, b) in enumerate(single):
+        for name, u, v in zip(("x", "y", "dx", "dy", "area", "angle"), a, b):
+            assert_bits(D.to_host(v), D.to_host(u), "band %d %s" % (k, name))
+    # flags did what the header says: the excluded top vertex row / the metrics stayed at the sentinel
+    assert (D.to_host(single[1][1][0])[-1] == -777.0).all() and (D.to_host(single[2][1][2]) == -777.0).all()
+    assert _cabi.load().ogg_band_fill_metrics_batch(bands, 5, ctypes.c_double(1.0), D.stream()) != 0   # > 4 bands: OGG_ERR_ARG
+
+
+def test_band_fill_non_finite_input(G, oracle):
+    """A NaN or infinite latitude / longitude leaves the band shortcuts (two constants for the angle, |t| for
+    the root): the fill must then produce what the general functions produce -- NaN where they do, finite values
+    elsewhere (assert_bits treats any two NaNs as equal, as everywhere in this suite)."""
+    from ocean_model_grid_generator_b200 import _cabi, device as D
+    lam = -300.0 + np.arange(97) * 360 / 96.0
+    phi = np.linspace(-60.0, 60.0, 21)
+    lam[13] = np.nan; lam[40] = np.inf; phi[5] = np.nan; phi[17] = -np.inf
+    nyp, nxp = phi.size, lam.size
+    o = _band_outputs(D, nyp, nxp)
+    tl, tp = D.to_dev(lam), D.to_dev(phi)
+    _cabi.call("ogg_band_fill_metrics", D.ptr(tl), D.ptr(tp), nyp, nxp, 6371.0e3, 0, *[D.ptr(t) for t in o], D.stream())
+    x, y = np.tile(lam, (nyp, 1)), np.tile(phi.reshape(-1, 1), (1, nxp))
+    with np.errstate(all="ignore"):
+        dx, dy, area = oracle.generate_grid_metrics_MIDAS(x, y)
+        ang = oracle.angle_x(x, y)
+    assert_bits(D.to_host(o[0]), x, "x"); assert_bits(D.to_host(o[1]), y, "y")
+    assert_bits(D.to_host(o[2]), dx, "dx"); assert_bits(D.to_host(o[3]), dy, "dy"); assert_bits(D.to_host(o[4]), area, "area")
+    assert_bits(D.to_host(o[5]), ang, "angle")
+    assert np.isnan(D.to_host(o[5])).any() and np.isfinite(D.to_host(o[5])).any()
+
+
 def test_quad_helpers(G, oracle):
     rng = np.random.default_rng(41)
     for n in (2, 3, 4, 5):
