@@ -191,6 +191,13 @@ int ogg_fp64_issue_rate(int64_t iters, double* ginstr_per_s_host);
  * is what this verifies.  Synchronous. */
 int ogg_selftest_divsqrt(int64_t n, uint64_t seed, int mode, uint64_t* counts3_host);
 
+/* ---- audit of the elided operand guards (csrc/ogg_trig.cuh, "ELIDE") -------------------------------------------------- */
+/* A library built with -DOGG_GUARD_AUDIT evaluates every operand-range claim the shipped build leaves out as proven and
+ * counts, over all cap-kernel launches on the current device since the last reset: counts2_host[0] = units (one projected
+ * vertex, one haversine, one quadrature sample) whose guard flag survived, [1] = those of them for which a claim was
+ * false (must be 0).  The shipped build returns {0, 0}.  reset != 0 clears the counters after reading.  Synchronous. */
+int ogg_guard_audit(uint64_t* counts2_host, int reset);
+
 #ifdef __cplusplus
 }
 #endif

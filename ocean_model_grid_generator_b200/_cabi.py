@@ -60,6 +60,7 @@ SIGNATURES = {
     "ogg_bswap64": [_vp, _vp, _i64, _vp],
     "ogg_fp64_issue_rate": [_i64, ctypes.POINTER(_d)],
     "ogg_selftest_divsqrt": [_i64, ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)],
+    "ogg_guard_audit": [ctypes.POINTER(ctypes.c_uint64), ctypes.c_int],
     "ogg_launch_count": [], "ogg_timing_enable": [_int], "ogg_timing_reset": [], "ogg_timing_kernels": [],
     "ogg_timing_name": [_int], "ogg_timing_get": [_int, ctypes.POINTER(_d), ctypes.POINTER(ctypes.c_longlong)],
     "ogg_timing_pair_span": [_int, _int, ctypes.POINTER(_d), ctypes.POINTER(ctypes.c_longlong)],

@@ -466,13 +466,22 @@ OGG_DI BpCol bp_col(double lamg, double lon_bp) {
   o.dl = lamg - lon_bp;
   return o;
 }
-// M: division / square-root policy (ogg_trig.cuh); with MathFast the caller must redo the sample if !m.ok()
+// M: division / square-root policy (ogg_trig.cuh); with MathFast the caller must redo the sample if !m.ok(), and its
+// base flag promises rp in [2**-63, 2**65) (bp_rp_ok).  The "proven" claims, in order:
+//  (1) alpha2 = ca*ca and beta2_inv = tb*tb are >= 0 or NaN, so 1 + alpha2*beta2_inv is >= 1, +inf or NaN: "not huge"
+//      is the whole guard.  (A NaN beta2_inv makes `huge` differ between the policies -- inside a failed unit.)
+//  (2) tan(chic/2) = s/c with s, c in "mid" and |s|, |c| <= 2: |tc| in [2**-130, 2**128], so |q| = |rp*tc| is in
+//      [2**-193, 2**193]: arctan's argument is not huge, 2*arctan(q) is in [2**-193, pi] (moderate), and 1 + q*q is in
+//      [1, 2**387] (moderate).
 template <bool FULL, class M>
 OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, double rp,
                       double& lams, double& phis, double& h_i_inv, double& h_j_inv) {
   const double alpha2 = C.alpha2, beta2_inv = R.beta2_inv;
-  const double rden = m.div_num_ok(1.0, 1.0 + alpha2 * beta2_inv);  // :47
-  const bool huge = fabs(beta2_inv) > kHuge;
+  const double den1 = 1.0 + alpha2 * beta2_inv;
+  m.require_not_huge(den1);
+  m.proven(rng_moderate(den1));                           // (1)
+  const double rden = m.div_ok(1.0, den1);               // :47
+  const bool huge = M::abs_gt_huge(beta2_inv);
   if (FULL) {
     double B = C.sinla * m.sqrt_(rden);                  // :50
     if (huge) B = 0.0;                                   // :52
@@ -487,10 +496,14 @@ OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, doubl
   }
   const double A = C.sinla * R.sphig;                    // :68
   const double chic = p_acos(m, A);                      // :69
-  const double tc = p_tan(m, chic / 2);
+  const double tc = p_tan<true>(m, chic / 2);
   const double q = rp * tc;
-  phis = 90 - m.div_pi180(2 * p_atan(m, q));             // :70
-  const double rden2 = m.div_num_ok(1.0, 1 + q * q);     // :72
+  const double at2 = 2 * p_atan<false>(m, q);            // (2)
+  m.proven(rng_moderate(at2));
+  phis = 90 - m.div_pi180_seq(at2);                      // :70
+  const double den2 = 1 + q * q;
+  m.proven(rng_moderate(den2));                          // (2)
+  const double rden2 = m.div_ok(1.0, den2);              // :72
   const double M_inv = (rp * (1 + tc * tc)) * rden2;     // :73
   const double cp = p_cos(m, phis * kPi180);
   const double cos2phis = cp * cp;                       // :79
@@ -503,6 +516,7 @@ OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, doubl
   if (huge) hi = MM;                                     // :94
   h_i_inv = m.sqrt_(hi);                                 // :95
 }
+OGG_DI bool bp_rp_ok(double rp) { const float f = hi_as_float(rp); return (f >= 0x1p-7f) && (f < 0x1p9f); }
 template <bool FULL>
 OGG_DI void bp_sample(const BpRow& R, const BpCol& C, double lon_bp, double rp, double& lams, double& phis,
                       double& h_i_inv, double& h_j_inv) {
@@ -744,6 +758,7 @@ __global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const
   const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
   // cached divisors pi/180, nx, ny (all moderate: nx, ny >= 1) with their refined reciprocals, stored by k_bp_quad_tables
   MathFast mf(divs);
+  mf.base = bp_rp_ok(rp);
   const MathFast::Divisor dnx = MathFast::load_divisor(divs + 2), dny = MathFast::load_divisor(divs + 4);
   // one sample: scaled h_i_inv, h_j_inv of unique row r / column c of this tile -> shared memory
   auto sample = [&](int r, int c, const BpCol& C, bool col_ok) {
@@ -754,7 +769,10 @@ __global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const
       double l, p;
       mf.reset();
       bp_sample<false>(mf, R, C, lon_bp, rp, l, p, a, b);
-      a = mf.div_by((a * 2) * kPi, dnx);                                         // :131
+      // a = sqrt_(hi) passed the square root's guard: it is in [2**-224, 2**225), and so is 2*pi times it
+      const double a2pi = (a * 2) * kPi;
+      mf.proven(rng_moderate(a2pi));
+      a = mf.div_by_seq(a2pi, dnx);                                              // :131
       b = mf.div_by((b * (90 - lat0_bp)) * kPi180, dny);                         // :132
       if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, the lon_bp meridian)
         const HiHj o = bp_qsample_ieee(R, C, lon_bp, rp, lat0_bp, (double)nx, (double)ny);
@@ -856,18 +874,24 @@ struct Cx { double re, im; };
 OGG_DI Cx cmul(Cx a, Cx b) { return Cx{a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }  // numpy, strict
 template <class M>
 OGG_DI Cx cdivn(M& m, Cx a, Cx b) {  // numpy CDOUBLE_divide (Smith)
-  const double abr = fabs(b.re), abi = fabs(b.im);
+  // MathFast: both parts of the divisor are held to the class "mid" (a zero part -- an axis crossing -- fails the unit).
+  // Then |rat| <= 1, the product b.im*rat = b.im**2/b.re has the sign of b.re and a magnitude in [2**-385, |b.re|], so
+  // the second divisor b.re + b.im*rat is in [|b.re|, 2|b.re|]: moderate, no guard of its own.
   Cx r;
-  if (abr >= abi) {
+  if (M::abs_ge(b.re, b.im)) {
     // (0,0) divisor: numpy's inf/nan rule; under MathFast a zero b.re fails the guard of the first division instead
-    if (!M::kFast && abr == 0 && abi == 0) { r.re = a.re / abr; r.im = a.im / abr; return r; }
-    const double rat = m.div(b.im, b.re);
-    const double scl = m.div_num_ok(1.0, b.re + b.im * rat);
+    if (!M::kFast && b.re == 0 && b.im == 0) { const double abr = fabs(b.re); r.re = a.re / abr; r.im = a.im / abr; return r; }
+    const double rat = m.div_mid(b.im, b.re);
+    const double den = b.re + b.im * rat;
+    m.proven(rng_moderate(den));
+    const double scl = m.div_ok(1.0, den);
     r.re = (a.re + a.im * rat) * scl;
     r.im = (a.im - a.re * rat) * scl;
   } else {
-    const double rat = m.div(b.re, b.im);
-    const double scl = m.div_num_ok(1.0, b.im + b.re * rat);
+    const double rat = m.div_mid(b.re, b.im);
+    const double den = b.im + b.re * rat;
+    m.proven(rng_moderate(den));
+    const double scl = m.div_ok(1.0, den);
     r.re = (a.re * rat + a.im) * scl;
     r.im = (a.im * rat - a.re) * scl;
   }
@@ -900,6 +924,32 @@ OGG_DI void dp_vertex(M& m, double r, Cx ep, const DpConst& K, double& lam_raw, 
 OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
   MathIeee m;
   dp_vertex(m, r, ep, K, lam_raw, phi);
+}
+// The same vertex under MathFast for k_dp_hsamples.  Preconditions, promised by the caller through m.base (k_dp_quad_setup
+// checks them once per table row / column): r, ep.re, ep.im and K.r_joint are in the class "mid" = [2**-127, 2**129).
+//  * ZEROOPS: z = (r + 0i) * e' in numpy's strict form is r*e'.re - 0*e'.im, r*e'.im + 0*e'.re.  With finite e' the
+//    products by 0 are +-0 and with r*e'.re, r*e'.im in [2**-254, 2**258] (non-zero) adding or subtracting them changes
+//    nothing; likewise 0.0 + q.im differs from q.im only for q.im = -0, where the divisor's imaginary part is a zero
+//    either way and the first division of cdivn fails the unit.  5 of a vertex's 146 FP64 operations.
+//  * p_atan2 holds w.re, w.im to "mid", so w.re**2 + w.im**2 is in [2**-254, 2**259] (the square root needs no guard
+//    of its own), rw * r_joint is in [2**-255, 2**260] (not huge) and its arctan in [2**-256, pi/2] (moderate).
+OGG_DI bool dp_mid(double v) { return rng_mid(v); }
+OGG_DI void dp_vertex_fast(MathFast& m, double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
+  Cx z = Cx{r * ep.re, r * ep.im};
+  if (!kZeroOps) z = cmul(Cx{r, 0.0}, ep);                                                   // :454
+#ifdef OGG_GUARD_AUDIT
+  { const Cx zz = cmul(Cx{r, 0.0}, ep);
+    m.proven(__double_as_longlong(zz.re) == __double_as_longlong(z.re) && __double_as_longlong(zz.im) == __double_as_longlong(z.im)); }
+#endif
+  const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
+  const Cx w = cdivn(m, Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, kZeroOps ? q.im : 0.0 + q.im});  // :455
+  lam_raw = p_atan2(m, w.im, w.re) * kC[k180OverPi];                                          // :457
+  const double ss = w.re * w.re + w.im * w.im;
+  m.proven(rng_pos_moderate(ss));
+  const double rw = m.sqrt_seq(ss);                                                          // :465
+  const double at = p_atan<false>(m, rw * K.r_joint);
+  m.proven(rng_moderate(at));
+  phi = -90 + m.div_pi180_seq(at);                                                           // :466
 }
 
 __global__ void k_dp_constants(double lat0, double lam_pole, double r_pole, double* __restrict__ out3) {
@@ -1025,7 +1075,8 @@ OGG_DI double haversine(M& m, double lam0, double phi0, double lam1, double phi1
   const double dphi = p1 - p0, dlam = l1 - l0;
   const double s1 = p_sin(m, 0.5 * dphi), s2 = p_sin(m, 0.5 * dlam);
   const double d = s1 * s1 + ((s2 * s2) * p_cos(m, p0)) * p_cos(m, p1);  // :531
-  return 2.0 * p_asin(m, m.sqrt_(d));                              // :532
+  // MathFast: d in [2**-127, 2**129) (coincident points -- d = 0 -- fail the unit), so its root is at least 2**-64
+  return 2.0 * p_asin<true>(m, m.sqrt_mid(d));                     // :532
 }
 OGG_DI double haversine(double lam0, double phi0, double lam1, double phi1) {
   MathIeee m;
@@ -1104,7 +1155,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
                                                                  i64 nrow, i64 ncol, const double* __restrict__ x0v,
                                                                  const double* __restrict__ cst, double reps,
                                                                  double* __restrict__ hx, double* __restrict__ hy,
-                                                                 unsigned long long* __restrict__ desc) {
+                                                                 unsigned long long* __restrict__ desc,
+                                                                 const int* __restrict__ tok) {
   constexpr int NM = 4 * NV, NT = 1 + 2 * NV, TW = THREADS - 1, kWarps = THREADS / 32;
   constexpr unsigned kMask = (1u << NM) - 1u;
   __shared__ double lamS[NM][THREADS];
@@ -1130,6 +1182,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
       // predicate around the loop, so its constants stay in uniform registers (-3 %)
       const Cx* cc = ct + (valid ? c : 0) * NT;
       const double* rr = rt + r * NT;
+      mf.base = (tok[valid ? c : 0] & tok[ncol + r]) != 0;             // dp_vertex_fast's preconditions
 #pragma unroll UNR
       for (int m = 0; m < NM; ++m) {
         const int lvl = m >> 2, kind = m & 3;
@@ -1137,7 +1190,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];            // e' at i +- (lvl+1) eps (kinds 0,1) or i
         double l, p;
         mf.reset();
-        dp_vertex(mf, rv, ep, K, l, p);
+        dp_vertex_fast(mf, rv, ep, K, l, p);
         if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, an axis crossing)
           const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
           l = o.l; p = o.p;
@@ -1153,27 +1206,48 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
     __syncthreads();
     Map2 mp{0u, 0xffffffffu};
     if (valid && threadIdx.x > 0) {
-      mp.f0 = 0u; mp.f1 = 0u;
+#ifndef OGG_NO_MAP_FAST
+      // |v - p| < 100 decides both tests without evaluating them: v - p > 100 is false, and v - fl(p - 360) lies within
+      // 1e-13 of (v - p) + 360 > 260, so the second is true -- the identity map.  Only a thread that sees a jump (or a
+      // NaN: its high word is above every finite one's) evaluates the reference's two differences.
+      int far = 0;
 #pragma unroll
-      for (int m = 0; m < NM; ++m) {
-        const double v = lamS[m][threadIdx.x], p = lamS[m][threadIdx.x - 1];
-        mp.f0 |= ((v - p) > 100 ? 1u : 0u) << m;
-        mp.f1 |= ((v - (p - 360)) > 100 ? 1u : 0u) << m;
+      for (int m = 0; m < NM; ++m)
+        far = max(far, __double2hiint(lamS[m][threadIdx.x] - lamS[m][threadIdx.x - 1]) & 0x7fffffff);
+      mp.f0 = 0u; mp.f1 = kMask;
+      if (far >= 0x40590000)   // |v - p| >= 100 (high word of 100.0; low word 0)
+#endif
+      {
+        mp.f0 = 0u; mp.f1 = 0u;
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+          const double v = lamS[m][threadIdx.x], p = lamS[m][threadIdx.x - 1];
+          mp.f0 |= ((v - p) > 100 ? 1u : 0u) << m;
+          mp.f1 |= ((v - (p - 360)) > 100 ? 1u : 0u) << m;
+        }
       }
     }
+#ifndef OGG_NO_SCAN_FAST
+    // a tile without a single +-360 jump (almost every tile: a row wraps once) has only identity maps: every prefix is
+    // the identity and the warp / block scans are skipped (the vote is the barrier the scan would need anyway)
+    const bool all_ident = __syncthreads_and(((mp.f0 & kMask) == 0u && (mp.f1 & kMask) == kMask) ? 1 : 0) != 0;
+    if (!all_ident)
+#endif
+    {
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      Map2 e;
-      e.f0 = __shfl_up_sync(0xffffffffu, mp.f0, off);
-      e.f1 = __shfl_up_sync(0xffffffffu, mp.f1, off);
-      if (lane >= (unsigned)off) mp = compose(e, mp);
-    }
-    if (lane == 31u) { shw[2 * warp] = mp.f0; shw[2 * warp + 1] = mp.f1; }
-    __syncthreads();
-    if (warp > 0) {
-      Map2 pre{shw[0], shw[1]};
-      for (unsigned w = 1; w < warp; ++w) pre = compose(pre, Map2{shw[2 * w], shw[2 * w + 1]});
-      mp = compose(pre, mp);
+      for (int off = 1; off < 32; off <<= 1) {
+        Map2 e;
+        e.f0 = __shfl_up_sync(0xffffffffu, mp.f0, off);
+        e.f1 = __shfl_up_sync(0xffffffffu, mp.f1, off);
+        if (lane >= (unsigned)off) mp = compose(e, mp);
+      }
+      if (lane == 31u) { shw[2 * warp] = mp.f0; shw[2 * warp + 1] = mp.f1; }
+      __syncthreads();
+      if (warp > 0) {
+        Map2 pre{shw[0], shw[1]};
+        for (unsigned w = 1; w < warp; ++w) pre = compose(pre, Map2{shw[2 * w], shw[2 * w + 1]});
+        mp = compose(pre, mp);
+      }
     }
     if (threadIdx.x == THREADS - 1) {
       unsigned s_in = 0u;
@@ -1296,7 +1370,18 @@ __global__ void __launch_bounds__(256) k_selftest_trig(i64 n, unsigned long long
     const unsigned long long h0 = splitmix64(seed + 2ull * (unsigned long long)e), h1 = splitmix64(h0 ^ 0x5851f42d4c957f2dull);
     const double u0 = (double)(h0 >> 11) * 0x1p-53, u1 = (double)(h1 >> 11) * 0x1p-53;   // [0, 1)
     const double scale = (h0 & 7) == 0 ? 1e-9 : 1.0;
-    const double x = (16.0 * u0 - 8.0) * scale, y = (16.0 * u1 - 8.0) * scale, c = (2.0 * u0 - 1.0) * scale;
+    double x = (16.0 * u0 - 8.0) * scale, y = (16.0 * u1 - 8.0) * scale, c = (2.0 * u0 - 1.0) * scale;
+    if (((h0 >> 3) & 15) == 1) {
+      // every 16th set sits on or within 2 ulps of a range boundary of arctan / arcsin / arccos (the integer-pipe
+      // comparisons of MathFast decide on the high word there), with either sign
+      const double edges[8] = {0.4375, 0.6875, 1.1875, 2.4375, 0.5, 1.0, 0.25, 2.0};
+      const double edge = edges[(h0 >> 7) & 7];
+      const long long off = (long long)((h0 >> 10) % 5) - 2;
+      const double v = __longlong_as_double(__double_as_longlong(edge) + off);
+      x = (h0 >> 20) & 1 ? -v : v;
+      c = x;
+      if ((h0 >> 21) & 1) y = x * ((h1 >> 5) & 1 ? 1.0 : -1.0);   // arctan2 with |y/x| = 1
+    }
     MathFast m;
     double v = p_tan(m, x);
     if (m.ok()) { ++acc; if (!same(v, p_tan(x))) ++bad; }
@@ -1876,7 +1961,8 @@ __global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i
                                                        double lon0, double lat0, double lam_pole, double r_pole, int nv,
                                                        double eps, double* __restrict__ cst, Cx* __restrict__ ct,
                                                        double* __restrict__ rt, double* __restrict__ x0v,
-                                                       unsigned long long* __restrict__ desc, i64 ndesc) {
+                                                       unsigned long long* __restrict__ desc, i64 ndesc,
+                                                       int* __restrict__ tok) {
   const i64 t = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   DpConst K;
   K.r_joint = p_tan((90 + lat0) * kPi180);                                                 // :494
@@ -1890,20 +1976,28 @@ __global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i
   const bool col = do_cols && t < nuc, row = t < nur;
   const double ic = col ? sample_index_at(q, order, 0, nx, nx, 0, t) : 0.0;                // :578-581
   const double jc = row ? sample_index_at(q, order, c0, c1, ny, 0, t) : 0.0;               // :573-576
+  // tok: dp_vertex_fast's preconditions, per table column [0, nuc) and per table row [nuc, nuc + nur)
+  bool col_ok = true, row_ok = dp_mid(K.r_joint);
   for (int k = 0; k < nt; ++k) {
     const int lvl = (k + 1) / 2;  // 0 centre, 1: eps, 2: 2eps, 3: 3eps
     const double s = lvl == 1 ? eps : (lvl == 2 ? 2.0 * eps : 3.0 * eps);
     const bool plus = (k & 1) == 1;
     if (col) {
       const double idx = k == 0 ? ic : (plus ? ic + s : ic - s);                           // :538,:541,:544
-      ct[t * nt + k] = dp_col(lon0 + (idx * 360.0) / (double)nx, K.z0);
+      const Cx e = dp_col(lon0 + (idx * 360.0) / (double)nx, K.z0);
+      ct[t * nt + k] = e;
+      col_ok = col_ok && dp_mid(e.re) && dp_mid(e.im);
     }
     if (row) {
       const double idx = k == 0 ? jc : (plus ? jc + s : jc - s);                           // :553,:556,:559
       const double a = -90.0, b = lat0;
-      rt[t * nt + k] = dp_row(a + (idx * (b - a)) / (double)ny, K.r_joint);
+      const double rv = dp_row(a + (idx * (b - a)) / (double)ny, K.r_joint);
+      rt[t * nt + k] = rv;
+      row_ok = row_ok && dp_mid(rv);
     }
   }
+  if (col) tok[t] = col_ok ? 1 : 0;
+  if (row) tok[nuc + t] = row_ok ? 1 : 0;
   if (do_cols && t < 4 * nv) {                                                             // x_0 of mesh t (k_dp_x0)
     const int lvl = (int)t / 4, kind = (int)t % 4;
     const double s = lvl == 0 ? eps : (lvl == 1 ? 2.0 * eps : 3.0 * eps);
@@ -1931,20 +2025,20 @@ static i64 dp_hsamples_items(int nv, i64 nrow, i64 ncol) {
 }
 template <int NV, int THREADS, int MINB, int UNR>
 static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
-                         double reps, double* hx, double* hy, unsigned long long* desc, cudaStream_t st) {
+                         double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, cudaStream_t st) {
   const i64 nitem = nrow * ((ncol + THREADS - 2) / (THREADS - 1));
   if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
   launch_begin(KID_DP_HSAMPLES, st);
-  k_dp_hsamples<NV, THREADS, MINB, UNR><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc);
+  k_dp_hsamples<NV, THREADS, MINB, UNR><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok);
   launch_end(st);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
 static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
-                       double reps, double* hx, double* hy, unsigned long long* desc, cudaStream_t st) {
-  if (nv == 1) return dp_hsamples_t<1, OGG_DP_THREADS, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
-  if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
-  return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, st);
+                       double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, cudaStream_t st) {
+  if (nv == 1) return dp_hsamples_t<1, OGG_DP_THREADS, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
+  if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
+  return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
 }
 }  // namespace ogg
 
@@ -2007,6 +2101,8 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
   OGG_CUDA(ws.get(&ct, nuc * nt)); OGG_CUDA(ws.get(&rt, max_nur * nt)); OGG_CUDA(ws.get(&x0v, 12));
   OGG_CUDA(ws.get(&sx, max_nur * nuc)); OGG_CUDA(ws.get(&sy, max_nur * nuc));
   OGG_CUDA(ws.get(&desc, (size_t)max_items + 1));
+  int* tok;
+  OGG_CUDA(ws.get(&tok, nuc + max_nur));
   int rc;
   for (i64 c0 = j0; c0 < j1; c0 += rows_per_chunk) {
     const i64 c1 = c0 + rows_per_chunk < j1 ? c0 + rows_per_chunk : j1;
@@ -2015,9 +2111,9 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
     const i64 ndesc = dp_hsamples_items(nv, nur, nuc) + 1;
     const i64 nthr = c0 == j0 ? (nuc > nur ? nuc : nur) : nur;
     OGG_LAUNCH(KID_DP_SETUP, (k_dp_quad_setup), (cdiv_u(nthr, 256), 256), (st), q, order, nx, ny, c0, c1, c0 == j0 ? 1 : 0,
-               lon0, lat0, lon_dp, r_dp, nv, eps, cst, ct, rt, x0v, desc, ndesc);
+               lon0, lat0, lon_dp, r_dp, nv, eps, cst, ct, rt, x0v, desc, ndesc, tok);
     OGG_LAUNCH_CHECK();
-    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, desc, st);
+    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, desc, tok, st);
     if (rc) return rc;
     rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
                         dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
@@ -2069,6 +2165,21 @@ int ogg_selftest_divsqrt(int64_t n, uint64_t seed, int mode, uint64_t* counts3_h
   cudaError_t e = cudaMemcpy(counts3_host, dev, 24, cudaMemcpyDeviceToHost);
   cudaFree(dev);
   OGG_CUDA(e);
+  return OGG_OK;
+}
+
+int ogg_guard_audit(uint64_t* counts2_host, int reset) {
+  if (!counts2_host) return OGG_ERR_ARG;
+  counts2_host[0] = counts2_host[1] = 0;
+#ifdef OGG_GUARD_AUDIT
+  OGG_CUDA(cudaDeviceSynchronize());
+  unsigned long long h[2] = {0ull, 0ull};
+  OGG_CUDA(cudaMemcpyFromSymbol(h, g_guard_audit, sizeof(h)));
+  counts2_host[0] = h[0]; counts2_host[1] = h[1];
+  if (reset) { h[0] = h[1] = 0ull; OGG_CUDA(cudaMemcpyToSymbol(g_guard_audit, h, sizeof(h))); }
+#else
+  (void)reset;
+#endif
   return OGG_OK;
 }
 

@@ -65,6 +65,31 @@ def test_fast_division_and_sqrt_are_ieee(G, mode):
     assert total > 0
 
 
+def test_elided_guards_audit(G):
+    """The cap kernels skip operand-range guards that follow from an earlier guard of the same unit (ELIDE, ZEROOPS in
+    csrc/ogg_trig.cuh / dp_vertex_fast).  A library built with -DOGG_GUARD_AUDIT evaluates every skipped claim while it
+    builds a set of supergrids and whole caps: no unit that passed its guards may have a false claim.  The shipped
+    library reports {0, 0} (its counters are compiled out)."""
+    import ctypes, json, os, shutil, subprocess, sys
+    from ocean_model_grid_generator_b200 import _cabi
+    counts = (ctypes.c_uint64 * 2)(7, 7)
+    assert _cabi.load().ogg_guard_audit(counts, 0) == 0 and counts[0] == 0 and counts[1] == 0
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "build", "libogg_audit.so")
+    src = [os.path.join(root, "ocean_model_grid_generator_b200", "csrc", f) for f in ("ogg_b200.cu", "ogg_trig.cuh")]
+    if not os.path.exists(lib) or any(os.path.getmtime(f) > os.path.getmtime(lib) for f in src):
+        if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+            pytest.skip("no nvcc to build the audit variant")
+        env = dict(os.environ, PATH=os.environ.get("PATH", "") + ":/usr/local/cuda/bin")
+        subprocess.check_call(["bash", os.path.join(root, "tools", "build_variant.sh"), "audit", "-DOGG_GUARD_AUDIT"], cwd=root, env=env)
+    env = dict(os.environ, OGG_B200_LIB=lib)
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "guard_audit.py")], cwd=root, env=env,
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    last = json.loads(out.stdout.strip().splitlines()[-1])
+    assert last["audit_build"] and last["units_passed"] > 10**8 and last["claims_false"] == 0, last
+
+
 def test_arctan2_and_mod(dnp, oracle):
     rng = np.random.default_rng(18)
     y, x = rng.uniform(-2, 2, 500000), rng.uniform(-2, 2, 500000)
