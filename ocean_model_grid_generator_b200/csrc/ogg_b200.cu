@@ -1110,9 +1110,39 @@ __global__ void __launch_bounds__(256) k_fd_combine(const double* __restrict__ d
 __device__ __noinline__ double haversine_ieee(double lam0, double phi0, double lam1, double phi1) {
   return haversine(lam0, phi0, lam1, phi1);
 }
+// The haversine of k_dp_hsamples.  Its four trigonometric calls share one straight-line block in the case every sample
+// of a real grid is in: the two half-differences are tiny (quadrant k = 0, where the Cody-Waite reduction subtracts three
+// exact zeros and returns its argument: skipped) and the two latitudes sit in an odd quadrant, so that all four values
+// come from the SINE polynomial -- evaluated four times on one set of coefficients in uniform registers, without the
+// per-call quadrant branches.  sin(dphi/2) and sin(dlam/2) enter :531 squared: their sign (and the sign of a zero
+// argument, the one thing the skipped reduction can change) does not reach the result.  Anything else takes the general
+// code; both give the bits of haversine<MathIeee> (tests: goldens, oracle parity, test_dp_haversine_quadrants).
 __device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam1, double phi1) {
   MathFast m;
+#ifndef OGG_NO_HAV_FAST
+  const double2 ra = m.pair(T_RED0), rb = m.pair(T_RED1);
+  const double l0 = lam0 * kPi180, p0 = phi0 * kPi180, l1 = lam1 * kPi180, p1 = phi1 * kPi180;
+  const double x1 = 0.5 * (p1 - p0), x2 = 0.5 * (l1 - l0);
+  const double k1 = rint(x1 * ra.x), k2 = rint(x2 * ra.x), k3 = rint(p0 * ra.x), k4 = rint(p1 * ra.x);
+  const int i1 = static_cast<int>(static_cast<long long>(k1)), i2 = static_cast<int>(static_cast<long long>(k2));
+  const int i3 = static_cast<int>(static_cast<long long>(k3)), i4 = static_cast<int>(static_cast<long long>(k4));
+  double d;
+  if ((i1 | i2) == 0 && (i3 & i4 & 1) != 0) {
+    const double r3 = ((p0 - k3 * ra.y) - k3 * rb.x) - k3 * rb.y;
+    const double r4 = ((p1 - k4 * ra.y) - k4 * rb.x) - k4 * rb.y;
+    const double s1 = sin_kernel(m, x1, x1 * x1), s2 = sin_kernel(m, x2, x2 * x2);
+    double c0 = sin_kernel(m, r3, r3 * r3), c1 = sin_kernel(m, r4, r4 * r4);
+    if ((i3 + 1) & 2) c0 = -c0;                                     // p_cos: quadrant n -> c, -s, -c, s
+    if ((i4 + 1) & 2) c1 = -c1;
+    d = s1 * s1 + ((s2 * s2) * c0) * c1;                            // :531
+  } else {
+    const double s1 = p_sin(m, x1), s2 = p_sin(m, x2);
+    d = s1 * s1 + ((s2 * s2) * p_cos(m, p0)) * p_cos(m, p1);
+  }
+  const double v = 2.0 * p_asin<true>(m, m.sqrt_mid(d));            // :532 (see haversine)
+#else
   const double v = haversine(m, lam0, phi0, lam1, phi1);
+#endif
   return m.ok() ? v : haversine_ieee(lam0, phi0, lam1, phi1);   // e.g. coincident points: sqrt(0), asin(0)
 }
 struct LamPhi { double l, p; };

@@ -204,6 +204,19 @@ def test_displaced_pole_vs_oracle(G, oracle, ni, nj, lon_dp, r_dp):
             assert_bits(g, r, "dp quad%d %s" % (order, n))
 
 
+@pytest.mark.parametrize("lat0,ni,nj", [(-20.0, 300, 12), (30.0, 520, 9), (-44.0, 64, 40), (80.0, 96, 6)])
+def test_dp_quad_haversine_quadrants(G, oracle, lat0, ni, nj):
+    """k_dp_hsamples' haversine has a straight-line path for latitudes in an odd quadrant of pi/2 (every real southern
+    cap: -90..-45 degrees) and the general code for the rest.  Caps reaching up to -44, -20, +30 and +80 degrees put
+    latitude pairs on both sides of the quadrant boundaries at -45 and +45 (mixed pairs take the general code); 300 and
+    520 columns span two and three look-back tiles, so the unwrap fast paths see tiles with and without the jump."""
+    lon0, lon_dp, r_dp = -300.0, 80.0, 0.2
+    for order in (2, 4):
+        for g, r, n in zip(G.displacedPoleCap_metrics_quad(order, ni, nj, lon0, lat0, lon_dp, r_dp),
+                           oracle.displacedPoleCap_metrics_quad(order, ni, nj, lon0, lat0, lon_dp, r_dp), ("dxq", "dyq", "daq")):
+            assert_bits(g, r, "dp quad%d lat0=%g %s" % (order, lat0, n))
+
+
 def test_monotonic_bounding_adversarial(G, oracle):
     """Random jumps exercise every branch of the 2-state scan, including chains where the shift state flips often,
     rows longer than one scan tile and values sitting on the 100-degree threshold."""
