@@ -422,11 +422,29 @@ __global__ void __launch_bounds__(256) k_dx_row(const double* __restrict__ xr, c
 }
 
 // angle_x (OGG:719-729)
+__device__ __noinline__ double angle_ieee(double dy, double dx, double yc) {
+  return p_atan2(dy, dx * p_cos(yc * kPi180)) / kPi180;
+}
+// pi180 != NULL: the two divisions of arctan2 and the one by pi/180 under MathFast, the compiler's code as redo (a zero
+// difference -- a grid line along a parallel or a meridian -- fails the unit)
 __global__ void __launch_bounds__(256) k_angle(const double* __restrict__ x, const double* __restrict__ y, i64 nyp,
-                                               i64 nxp, double* __restrict__ angle) {
+                                               i64 nxp, double* __restrict__ angle, const double* __restrict__ pi180) {
   const i64 i = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   if (i >= nxp) return;
   const i64 ia = i == nxp - 1 ? i : i + 1, ib = i == 0 ? i : i - 1;
+  if (pi180) {
+    MathFast mf(pi180);
+    for (i64 j = blockIdx.y; j < nyp; j += gridDim.y) {
+      const double* xr = x + j * nxp;
+      const double* yr = y + j * nxp;
+      const double dy = yr[ia] - yr[ib], dx = xr[ia] - xr[ib], yc = yr[i];
+      mf.reset();
+      double a = mf.div_pi180(p_atan2(mf, dy, dx * p_cos(mf, yc * kPi180)));
+      if (!mf.ok()) a = angle_ieee(dy, dx, yc);
+      angle[j * nxp + i] = a;
+    }
+    return;
+  }
   for (i64 j = blockIdx.y; j < nyp; j += gridDim.y) {
     const double* xr = x + j * nxp;
     const double* yr = y + j * nxp;
@@ -473,7 +491,7 @@ OGG_DI BpCol bp_col(double lamg, double lon_bp) {
 //  (2) tan(chic/2) = s/c with s, c in "mid" and |s|, |c| <= 2: |tc| in [2**-130, 2**128], so |q| = |rp*tc| is in
 //      [2**-193, 2**193]: arctan's argument is not huge, 2*arctan(q) is in [2**-193, pi] (moderate), and 1 + q*q is in
 //      [1, 2**387] (moderate).
-template <bool FULL, class M>
+template <bool FULL, class M, bool METRICS = true>
 OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, double rp,
                       double& lams, double& phis, double& h_i_inv, double& h_j_inv) {
   const double alpha2 = C.alpha2, beta2_inv = R.beta2_inv;
@@ -496,16 +514,17 @@ OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, doubl
   }
   const double A = C.sinla * R.sphig;                    // :68
   const double chic = p_acos(m, A);                      // :69
-  const double tc = p_tan<true>(m, chic / 2);
+  const double tc = p_tan_q0<true>(m, chic / 2);        // chic in [0, pi]: quadrant 0 unless A < 0 (never on a cap)
   const double q = rp * tc;
   const double at2 = 2 * p_atan<false>(m, q);            // (2)
   m.proven(rng_moderate(at2));
   phis = 90 - m.div_pi180_seq(at2);                      // :70
+  if (!METRICS) { h_i_inv = 0.0; h_j_inv = 0.0; return; } // coordinates only (the supergrid takes the metrics from the quadrature)
   const double den2 = 1 + q * q;
   m.proven(rng_moderate(den2));                          // (2)
   const double rden2 = m.div_ok(1.0, den2);              // :72
   const double M_inv = (rp * (1 + tc * tc)) * rden2;     // :73
-  const double cp = p_cos(m, phis * kPi180);
+  const double cp = p_cos_q1_unsigned(m, phis * kPi180);  // +-cos(phis): squared on the next line
   const double cos2phis = cp * cp;                       // :79
   const double MM = M_inv * M_inv, r2 = rden * rden;
   double hj = ((((cos2phis * alpha2) * (1 - alpha2)) * beta2_inv) * (1 + beta2_inv)) * r2 +
@@ -557,14 +576,22 @@ __global__ void __launch_bounds__(256) k_bp_tables(const double* __restrict__ iv
   }
 }
 
+struct HiHj { double a, b; };
+__device__ __noinline__ HiHj bp_vertex_ieee(BpRow R, BpCol C, double lon_bp, double rp) {   // (lams, phis), compiler's / and sqrt
+  double l, p, a, b;
+  MathIeee m;
+  bp_sample<true, MathIeee, false>(m, R, C, lon_bp, rp, l, p, a, b);
+  return HiHj{l, p};
+}
 // MODE 0: mesh (:118-120): lams, phis + optionally scaled h's with the mesh's trimming
+// MODE 2: lams, phis only (pi180: the cached divisor pair of pi180_pair())
 // MODE 1: metrics-only samples (:130-132): scaled h_i_inv, h_j_inv on the full lattice
 template <int MODE>
 __global__ void __launch_bounds__(256) k_bp_lattice(const BpCol* __restrict__ ct, const BpRow* __restrict__ rt,
                                                     i64 nrow, i64 ncol, i64 Ni, i64 Nj, i64 jrow0, double lat0_bp,
                                                     double lon_bp, double rp, double* __restrict__ o0,
                                                     double* __restrict__ o1, double* __restrict__ o2,
-                                                    double* __restrict__ o3) {
+                                                    double* __restrict__ o3, const double* __restrict__ pi180) {
   const i64 c = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   if (c >= ncol) return;
   const BpCol C = ct[c];
@@ -577,6 +604,15 @@ __global__ void __launch_bounds__(256) k_bp_lattice(const BpCol* __restrict__ ct
       o1[r * ncol + c] = p;
       if (o2 && c < ncol - 1) o2[r * (ncol - 1) + c] = ((a * 2) * kPi) / (double)Ni;                        // :119
       if (o3 && jrow0 + r < Nj) o3[r * ncol + c] = ((b * kPi180) * (90 - lat0_bp)) / (double)Nj;            // :120
+    } else if (MODE == 2) {
+      // coordinates only, under MathFast (the supergrid's cap mesh: its metrics come from the quadrature)
+      MathFast mf(pi180);
+      mf.base = bp_rp_ok(rp);
+      mf.reset();
+      bp_sample<true, MathFast, false>(mf, R, C, lon_bp, rp, l, p, a, b);
+      if (!mf.ok()) { const HiHj o = bp_vertex_ieee(R, C, lon_bp, rp); l = o.a; p = o.b; }
+      o0[r * ncol + c] = l;
+      o1[r * ncol + c] = p;
     } else {
       bp_sample<false>(R, C, lon_bp, rp, l, p, a, b);
       o0[r * ncol + c] = ((a * 2) * kPi) / (double)Ni;                                                      // :131
@@ -732,7 +768,6 @@ __global__ void __launch_bounds__(256) k_bp_quad_tables(QuadNodes q, int n, i64 
 #ifndef OGG_BP_MINB
 #define OGG_BP_MINB 4
 #endif
-struct HiHj { double a, b; };
 __device__ __noinline__ HiHj bp_qsample_ieee(BpRow R, BpCol C, double lon_bp, double rp, double lat0_bp, double dnx,
                                              double dny) {
   double l, p, a, b;
@@ -952,6 +987,12 @@ OGG_DI void dp_vertex_fast(MathFast& m, double r, Cx ep, const DpConst& K, doubl
   phi = -90 + m.div_pi180_seq(at);                                                           // :466
 }
 
+struct LamPhi { double l, p; };
+__device__ __noinline__ LamPhi dp_vertex_ieee(double r, double epre, double epim, double rj, double z0re, double z0im) {
+  LamPhi o;
+  dp_vertex(r, Cx{epre, epim}, DpConst{rj, Cx{z0re, z0im}}, o.l, o.p);
+  return o;
+}
 __global__ void k_dp_constants(double lat0, double lam_pole, double r_pole, double* __restrict__ out3) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     out3[0] = p_tan((90 + lat0) * kPi180);                                                   // :494
@@ -993,13 +1034,30 @@ __global__ void __launch_bounds__(256) k_dp_tables(const double* __restrict__ iv
     rt[t] = dp_row(a + (idx * (b - a)) / (double)nj, K.r_joint);
   }
 }
+// pi180 != NULL: MathFast (dp_vertex_fast; its preconditions are checked here per vertex) with the compiler's code as redo
 __global__ void __launch_bounds__(256) k_dp_lattice_raw(const Cx* __restrict__ ct, const double* __restrict__ rt,
                                                         i64 nrow, i64 ncol, const double* __restrict__ cst,
-                                                        double* __restrict__ lam, double* __restrict__ phi) {
+                                                        double* __restrict__ lam, double* __restrict__ phi,
+                                                        const double* __restrict__ pi180) {
   const i64 c = blockIdx.x * (i64)blockDim.x + threadIdx.x;
   if (c >= ncol) return;
   const DpConst K = dp_load(cst);
   const Cx ep = ct[c];
+  if (pi180) {
+    MathFast mf(pi180);
+    const bool col_ok = dp_mid(ep.re) && dp_mid(ep.im) && dp_mid(K.r_joint);
+    for (i64 r = blockIdx.y; r < nrow; r += gridDim.y) {
+      const double rv = rt[r];
+      double l, p;
+      mf.base = col_ok && dp_mid(rv);
+      mf.reset();
+      dp_vertex_fast(mf, rv, ep, K, l, p);
+      if (!mf.ok()) { const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im); l = o.l; p = o.p; }
+      lam[r * ncol + c] = l;
+      phi[r * ncol + c] = p;
+    }
+    return;
+  }
   for (i64 r = blockIdx.y; r < nrow; r += gridDim.y) dp_vertex(rt[r], ep, K, lam[r * ncol + c], phi[r * ncol + c]);
 }
 
@@ -1144,12 +1202,6 @@ __device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam
   const double v = haversine(m, lam0, phi0, lam1, phi1);
 #endif
   return m.ok() ? v : haversine_ieee(lam0, phi0, lam1, phi1);   // e.g. coincident points: sqrt(0), asin(0)
-}
-struct LamPhi { double l, p; };
-__device__ __noinline__ LamPhi dp_vertex_ieee(double r, double epre, double epim, double rj, double z0re, double z0im) {
-  LamPhi o;
-  dp_vertex(r, Cx{epre, epim}, DpConst{rj, Cx{z0re, z0im}}, o.l, o.p);
-  return o;
 }
 // --- fused numerical_hi + numerical_hj on a lattice of unique samples (OGG:583-584) ------------------------------
 // For finite-difference order 2*NV there are 4*NV shifted meshes (i+-m*eps at this row; j+-m*eps at this column),
@@ -1519,6 +1571,29 @@ __global__ void __launch_bounds__(256) k_fp64_rate(i64 iters, double seed, doubl
 // ------------------------------------------------------------------------------------------------
 // host-side composition helpers
 // ------------------------------------------------------------------------------------------------
+// pi/180 with its refined reciprocal (MathFast::Divisor) in device memory, computed once per device: the short mesh /
+// angle kernels divide by it under MathFast without a set-up launch of their own.
+__global__ void k_store_pi180(double* __restrict__ by) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) MathFast::store_divisor(by, kPi180);
+}
+static const double* pi180_pair() {
+  static double* pairs[kMaxDevices] = {nullptr};
+  static std::mutex mu;
+  const int dev = current_device();
+  std::lock_guard<std::mutex> lock(mu);
+  if (!pairs[dev]) {
+    double* d = nullptr;
+    cudaStream_t st = nullptr;
+    if (cudaMalloc(&d, 2 * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); cudaFree(d); return nullptr; }
+    k_store_pi180<<<1, 32, 0, st>>>(d);
+    const cudaError_t e = cudaStreamSynchronize(st);   // visible to every stream before the pointer is handed out
+    cudaStreamDestroy(st);
+    if (e != cudaSuccess) { cudaGetLastError(); cudaFree(d); return nullptr; }
+    pairs[dev] = d;
+  }
+  return pairs[dev];
+}
 static dim3 lattice_grid(i64 ncol, i64 nrow, int threads) {
   const unsigned gx = cdiv_u(ncol, threads);
   i64 gy = ((i64)num_sms() * 16 + gx - 1) / gx;
@@ -1780,7 +1855,7 @@ int ogg_metrics_midas(const double* x, const double* y, int64_t nyp, int64_t nxp
 
 int ogg_angle_x(const double* x, const double* y, int64_t nyp, int64_t nxp, double* angle, void* stream) {
   if (!x || !y || !angle || nyp < 1 || nxp < 2) return OGG_ERR_ARG;
-  OGG_LAUNCH(KID_ANGLE, (k_angle), (lattice_grid(nxp, nyp, 256), 256), (S(stream)), x, y, nyp, nxp, angle);
+  OGG_LAUNCH(KID_ANGLE, (k_angle), (lattice_grid(nxp, nyp, 256), 256), (S(stream)), x, y, nyp, nxp, angle, pi180_pair());
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1806,8 +1881,13 @@ int ogg_bipolar_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double 
   const i64 m = ncol > nrow ? ncol : nrow;
   OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(m, 256), 256), (st), nullptr, 0, ncol, nullptr, j0, nrow, Ni, Nj, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
-  OGG_LAUNCH(KID_BP_MESH, (k_bp_lattice<0>), (lattice_grid(ncol, nrow, 256), 256), (st), ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
-                                                                 phis, h_i_inv, h_j_inv);
+  const double* pi180 = (!h_i_inv && !h_j_inv) ? pi180_pair() : nullptr;
+  if (pi180)   // coordinates only: no metrics evaluated, division / square root without branches
+    OGG_LAUNCH(KID_BP_MESH, (k_bp_lattice<2>), (lattice_grid(ncol, nrow, 256), 256), (st), ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
+                                                                   phis, h_i_inv, h_j_inv, pi180);
+  else
+    OGG_LAUNCH(KID_BP_MESH, (k_bp_lattice<0>), (lattice_grid(ncol, nrow, 256), 256), (st), ct, rt, nrow, ncol, Ni, Nj, j0, lat0_bp, lon_bp, rp, lams,
+                                                                   phis, h_i_inv, h_j_inv, pi180);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1823,7 +1903,7 @@ int ogg_bipolar_cap_ij_array(const double* i, int64_t ni, const double* j, int64
   OGG_LAUNCH(KID_BP_TABLES, (k_bp_tables), (cdiv_u(m, 256), 256), (st), i, 0, ni, j, 0, nj, Ni, Nj_ncap, lat0_bp, lon_bp, rp, ct, rt);
   OGG_LAUNCH_CHECK();
   OGG_LAUNCH(KID_BP_SAMPLES, (k_bp_lattice<1>), (lattice_grid(ni, nj, 256), 256), (st), ct, rt, nj, ni, Ni, Nj_ncap, 0, lat0_bp, lon_bp, rp, h_i_inv,
-                                                             h_j_inv, nullptr, nullptr);
+                                                             h_j_inv, nullptr, nullptr, nullptr);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
@@ -1919,7 +1999,7 @@ static int dp_mesh_dev(const double* iv, i64 i0, i64 nil, double ishift, const d
   const i64 m = nil > njl ? nil : njl;
   OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables), (cdiv_u(m, 256), 256), (st), iv, i0, nil, ishift, jv, j0, njl, jshift, ni, nj, lon0, lat0, cst, ct, rt);
   OGG_LAUNCH_CHECK();
-  OGG_LAUNCH(KID_DP_RAW, (k_dp_lattice_raw), (lattice_grid(nil, njl, 256), 256), (st), ct, rt, njl, nil, cst, lams, phis);
+  OGG_LAUNCH(KID_DP_RAW, (k_dp_lattice_raw), (lattice_grid(nil, njl, 256), 256), (st), ct, rt, njl, nil, cst, lams, phis, pi180_pair());
   OGG_LAUNCH_CHECK();
   // x_0 = lon_grid[0,0] = lon0 + ((i[0]+shift)*360)/ni : reuse k_dp_x0<1> slots (kind 0 = plus shift, kind 2 = none)
   OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), iv, (double)i0, ishift, ni, lon0, x0);
