@@ -499,7 +499,10 @@ OGG_DI void bp_sample(M& m, const BpRow& R, const BpCol& C, double lon_bp, doubl
   m.require_not_huge(den1);
   m.proven(rng_moderate(den1));                           // (1)
   const double rden = m.div_ok(1.0, den1);               // :47
-  const bool huge = M::abs_gt_huge(beta2_inv);
+  // |beta2_inv| > 1e30 happens on the exact pole row only: under MathFast it fails the unit (the redo applies :52, :86,
+  // :94) instead of costing every sample a compare and five selects
+  const bool huge = M::kFast ? false : M::abs_gt_huge(beta2_inv);
+  if (M::kFast) m.require(fabsf(hi_as_float(beta2_inv)) < 0x1p13f);   // high word of 2**97 < 1e30; a NaN fails too
   if (FULL) {
     double B = C.sinla * m.sqrt_(rden);                  // :50
     if (huge) B = 0.0;                                   // :52
@@ -907,13 +910,16 @@ __global__ void __launch_bounds__(128) k_quad_avg2d(const double* __restrict__ y
 // ------------------------------------------------------------------------------------------------
 struct Cx { double re, im; };
 OGG_DI Cx cmul(Cx a, Cx b) { return Cx{a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }  // numpy, strict
-template <class M>
+// RE_DOMINANT (MathFast only): the caller expects |b.re| >= |b.im| -- anything else fails the unit -- and the other
+// branch of Smith's algorithm is not compiled in.
+template <bool RE_DOMINANT = false, class M>
 OGG_DI Cx cdivn(M& m, Cx a, Cx b) {  // numpy CDOUBLE_divide (Smith)
   // MathFast: both parts of the divisor are held to the class "mid" (a zero part -- an axis crossing -- fails the unit).
   // Then |rat| <= 1, the product b.im*rat = b.im**2/b.re has the sign of b.re and a magnitude in [2**-385, |b.re|], so
   // the second divisor b.re + b.im*rat is in [|b.re|, 2|b.re|]: moderate, no guard of its own.
   Cx r;
-  if (M::abs_ge(b.re, b.im)) {
+  if (RE_DOMINANT) m.require(M::abs_ge(b.re, b.im));
+  if (RE_DOMINANT || M::abs_ge(b.re, b.im)) {
     // (0,0) divisor: numpy's inf/nan rule; under MathFast a zero b.re fails the guard of the first division instead
     if (!M::kFast && b.re == 0 && b.im == 0) { const double abr = fabs(b.re); r.re = a.re / abr; r.im = a.im / abr; return r; }
     const double rat = m.div_mid(b.im, b.re);
@@ -969,6 +975,12 @@ OGG_DI void dp_vertex(double r, Cx ep, const DpConst& K, double& lam_raw, double
 //  * p_atan2 holds w.re, w.im to "mid", so w.re**2 + w.im**2 is in [2**-254, 2**259] (the square root needs no guard
 //    of its own), rw * r_joint is in [2**-255, 2**260] (not huge) and its arctan in [2**-256, pi/2] (moderate).
 OGG_DI bool dp_mid(double v) { return rng_mid(v); }
+//  * SMALLAT (the host sets it for caps that end south of 67 S with a pole displaced by at most half the cap's radius:
+//    every southern cap the reference's recipes make): tan(phi + 90) < 0.4375 at every vertex, so the latitude's arctan
+//    is taken in its first range without the range selection (r_joint > 0 is then part of the caller's promise: the
+//    argument rw * r_joint is positive -- no |x|, no copysign), and Smith's division takes its first branch.  A vertex
+//    that is not like that fails its unit and is redone: the flag is about speed, never about results.
+template <bool SMALLAT = false>
 OGG_DI void dp_vertex_fast(MathFast& m, double r, Cx ep, const DpConst& K, double& lam_raw, double& phi) {
   Cx z = Cx{r * ep.re, r * ep.im};
   if (!kZeroOps) z = cmul(Cx{r, 0.0}, ep);                                                   // :454
@@ -977,12 +989,13 @@ OGG_DI void dp_vertex_fast(MathFast& m, double r, Cx ep, const DpConst& K, doubl
     m.proven(__double_as_longlong(zz.re) == __double_as_longlong(z.re) && __double_as_longlong(zz.im) == __double_as_longlong(z.im)); }
 #endif
   const Cx q = cmul(Cx{K.z0.re, -K.z0.im}, z);
-  const Cx w = cdivn(m, Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, kZeroOps ? q.im : 0.0 + q.im});  // :455
+  // SMALLAT caps have |z0| <= 0.5 and |z| <= 1 (+ eps): the divisor 1 + conj(z0) z has the dominant real part
+  const Cx w = cdivn<SMALLAT>(m, Cx{z.re + K.z0.re, z.im + K.z0.im}, Cx{1.0 + q.re, kZeroOps ? q.im : 0.0 + q.im});  // :455
   lam_raw = p_atan2(m, w.im, w.re) * kC[k180OverPi];                                          // :457
   const double ss = w.re * w.re + w.im * w.im;
   m.proven(rng_pos_moderate(ss));
   const double rw = m.sqrt_seq(ss);                                                          // :465
-  const double at = p_atan<false>(m, rw * K.r_joint);
+  const double at = SMALLAT ? atan_first_range(m, rw * K.r_joint) : p_atan<false>(m, rw * K.r_joint);
   m.proven(rng_moderate(at));
   phi = -90 + m.div_pi180_seq(at);                                                           // :466
 }
@@ -1197,7 +1210,9 @@ __device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam
     const double s1 = p_sin(m, x1), s2 = p_sin(m, x2);
     d = s1 * s1 + ((s2 * s2) * p_cos(m, p0)) * p_cos(m, p1);
   }
-  const double v = 2.0 * p_asin<true>(m, m.sqrt_mid(d));            // :532 (see haversine)
+  // :532; d in [2**-127, 2**129) or the unit fails, so its root is at least 2**-64; a root of 0.5 or more (points more
+  // than 60 degrees apart) fails the unit too
+  const double v = 2.0 * p_asin_small_pos(m, m.sqrt_mid(d));
 #else
   const double v = haversine(m, lam0, phi0, lam1, phi1);
 #endif
@@ -1232,7 +1247,7 @@ OGG_DI void desc_store(unsigned long long* p, unsigned long long v) {
 // rolled loops: fewer live registers, and less code than the fully unrolled form (which misses the instruction cache).
 // Items are numbered tile-major (all rows' tile t before any tile t+1), so that a tile's left neighbour was drawn
 // nrow tickets earlier and its descriptor is normally there when looked for.
-template <int NV, int THREADS, int MINB, int UNR>
+template <int NV, int THREADS, int MINB, int UNR, bool SMALLAT>
 __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restrict__ ct, const double* __restrict__ rt,
                                                                  i64 nrow, i64 ncol, const double* __restrict__ x0v,
                                                                  const double* __restrict__ cst, double reps,
@@ -1264,7 +1279,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
       // predicate around the loop, so its constants stay in uniform registers (-3 %)
       const Cx* cc = ct + (valid ? c : 0) * NT;
       const double* rr = rt + r * NT;
-      mf.base = (tok[valid ? c : 0] & tok[ncol + r]) != 0;             // dp_vertex_fast's preconditions
+      mf.base = (tok[valid ? c : 0] & tok[ncol + r]) != 0 && (!SMALLAT || K.r_joint > 0.0);   // dp_vertex_fast's preconditions
 #pragma unroll UNR
       for (int m = 0; m < NM; ++m) {
         const int lvl = m >> 2, kind = m & 3;
@@ -1272,7 +1287,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];            // e' at i +- (lvl+1) eps (kinds 0,1) or i
         double l, p;
         mf.reset();
-        dp_vertex_fast(mf, rv, ep, K, l, p);
+        dp_vertex_fast<SMALLAT>(mf, rv, ep, K, l, p);
         if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, an axis crossing)
           const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
           l = o.l; p = o.p;
@@ -2125,6 +2140,9 @@ __global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i
 #ifndef OGG_DP_UNR
 #define OGG_DP_UNR 4
 #endif
+#ifndef OGG_DP_UNR_SA  // the SMALLAT instantiation's loop body is shorter: all 8 meshes unrolled fit the instruction cache
+#define OGG_DP_UNR_SA 8
+#endif
 #ifndef OGG_DP_THREADS
 #define OGG_DP_THREADS 256
 #endif
@@ -2133,19 +2151,23 @@ static i64 dp_hsamples_items(int nv, i64 nrow, i64 ncol) {
   const int threads = nv == 3 ? 128 : OGG_DP_THREADS;
   return nrow * ((ncol + threads - 2) / (threads - 1));
 }
-template <int NV, int THREADS, int MINB, int UNR>
+template <int NV, int THREADS, int MINB, int UNR, bool SMALLAT = false>
 static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
                          double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, cudaStream_t st) {
   const i64 nitem = nrow * ((ncol + THREADS - 2) / (THREADS - 1));
   if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
   launch_begin(KID_DP_HSAMPLES, st);
-  k_dp_hsamples<NV, THREADS, MINB, UNR><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok);
+  k_dp_hsamples<NV, THREADS, MINB, UNR, SMALLAT><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok);
   launch_end(st);
   OGG_LAUNCH_CHECK();
   return OGG_OK;
 }
 static int dp_hsamples(int nv, const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
-                       double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, cudaStream_t st) {
+                       double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, bool small_at, cudaStream_t st) {
+#ifndef OGG_NO_SMALLAT
+  if (nv == 2 && small_at)
+    return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR_SA, true>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
+#endif
   if (nv == 1) return dp_hsamples_t<1, OGG_DP_THREADS, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
   if (nv == 2) return dp_hsamples_t<2, OGG_DP_THREADS, OGG_DP_MINB, OGG_DP_UNR>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
   return dp_hsamples_t<3, 128, 4, 4>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok, st);
@@ -2223,7 +2245,7 @@ int ogg_dp_metrics_quad(int order, int64_t nx, int64_t ny, int64_t j0, int64_t j
     OGG_LAUNCH(KID_DP_SETUP, (k_dp_quad_setup), (cdiv_u(nthr, 256), 256), (st), q, order, nx, ny, c0, c1, c0 == j0 ? 1 : 0,
                lon0, lat0, lon_dp, r_dp, nv, eps, cst, ct, rt, x0v, desc, ndesc, tok);
     OGG_LAUNCH_CHECK();
-    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, desc, tok, st);
+    rc = dp_hsamples(nv, ct, rt, nur, nuc, x0v, cst, 1.0 / eps, sx, sy, desc, tok, lat0 < -67.0 && fabs(r_dp) <= 0.5, st);
     if (rc) return rc;
     rc = run_quad_cells(order, sx, sy, nuc, c1 - c0, nx, top ? nur - 1 : -1, Re, dxq + (c0 - j0) * nx,
                         dyq + (c0 - j0) * (nx + 1), daq + (c0 - j0) * nx, st);
