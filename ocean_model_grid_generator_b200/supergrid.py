@@ -229,7 +229,9 @@ def _stream_pool():
         # measured at r=4 (tools/stepbench.py): all equal 0.977 ms, short kernels above the quadratures 0.972, and the
         # second cap's quadrature (the cheaper bipolar one, which then finishes first and frees the SMs for the
         # displaced-pole tail) above the first 0.966
-        _POOL[dev] = ([torch.cuda.Stream(priority=0), torch.cuda.Stream(priority=-1)] +
+        import os
+        p0, p1 = {"first": (-1, 0), "equal": (0, 0)}.get(os.environ.get("OGG_QUAD_PRIO", ""), (0, -1))   # A/B knob
+        _POOL[dev] = ([torch.cuda.Stream(priority=p0), torch.cuda.Stream(priority=p1)] +
                       [torch.cuda.Stream(priority=-2) for _ in range(4)], [torch.cuda.Event() for _ in range(8)])
     return _POOL[dev]
 
