@@ -20,6 +20,8 @@ assert lib.ogg_guard_audit(counts, 1) == 0
 RECIPES = ["-r 4 --r_dp 0.2", "-r 1", "-r 2 --r_dp 0.2 --south_cutoff_row 2", "-r 1.5 --r_dp 0.05 --lon_dp 123.0",
            "-r 3 --r_dp 0.6 --lon_dp 10.0", "-r 2 --lat_dp -85.85", "-r 0.5 --r_dp 0.9",
            "-r 8 --r_dp 0.2 --south_cutoff_row 5 --match_dy bp so p125sc --ensure_nj_even"]
+if "--big" in sys.argv:   # soak: the 1/12- and 1/30-degree grids (1.1e9 and 6.7e9 samples)
+    RECIPES = ["-r 12 --r_dp 0.2", "-r 30 --r_dp 0.2 --ensure_nj_even"]
 out = []
 for rec in RECIPES:
     try:
@@ -34,7 +36,9 @@ for rec in RECIPES:
     torch.cuda.synchronize()
     assert lib.ogg_guard_audit(counts, 1) == 0
     out.append({"recipe": rec, "units_passed": int(counts[0]), "claims_false": int(counts[1])})
-    print(json.dumps(out[-1]))
+    print(json.dumps(out[-1]), flush=True)
+    del sg
+    torch.cuda.empty_cache()
 # whole caps incl. the pole rows (the supergrid recipes above cut the displaced-pole cap's inner rows away)
 for order, Ni, Nj in ((4, 1440, 140), (2, 360, 35)):
     sx, sy, sa = D.empty(Nj + 1, Ni), D.empty(Nj, Ni + 1), D.empty(Nj, Ni)
