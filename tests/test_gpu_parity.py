@@ -217,6 +217,45 @@ def test_dp_quad_haversine_quadrants(G, oracle, lat0, ni, nj):
             assert_bits(g, r, "dp quad%d lat0=%g %s" % (order, lat0, n))
 
 
+def test_random_caps_vs_oracle(G, oracle):
+    """Seeded random cap geometries through both fused quadratures and both cap meshes against the oracle, bit for bit.
+    The draws cover what the kernels specialise on: southern caps that take the first-range arctan / first Smith branch
+    (lat0 < -67, r_dp <= 0.5) and caps that do not, poles displaced almost to the cap edge, bipolar caps starting at 40 to
+    85 degrees (latitudes on both sides of quadrant 1 of the cosine path), column counts around the 255-column look-back
+    tile and the 32-cell bipolar tile, every coded order."""
+    rng = np.random.default_rng(20261105)
+    for trial in range(10):
+        order = int(rng.choice([2, 4]))
+        ni = int(rng.choice([8, 31, 85, 86, 170, 171, 300]))
+        nj = int(rng.integers(2, 14))
+        lon0 = float(rng.uniform(-360, 360))
+        lat0 = float(rng.choice([-80.0, -67.0, -66.9, -45.0, 10.0, 75.0])) + float(rng.uniform(-1, 1)) * (trial % 2)
+        lon_dp = float(rng.uniform(-180, 180))
+        r_dp = float(rng.choice([0.01, 0.2, 0.5, 0.51, 0.95]))
+        what = "dp trial %d: order %d ni %d nj %d lon0 %r lat0 %r lon_dp %r r_dp %r" % (trial, order, ni, nj, lon0, lat0, lon_dp, r_dp)
+        for g, r, n in zip(G.displacedPoleCap_metrics_quad(order, ni, nj, lon0, lat0, lon_dp, r_dp),
+                           oracle.displacedPoleCap_metrics_quad(order, ni, nj, lon0, lat0, lon_dp, r_dp), ("dxq", "dyq", "daq")):
+            assert_bits(g, r, what + " " + n)
+        for g, r, n in zip(G.generate_displaced_pole_grid(ni, nj, lon0, lat0, lon_dp, r_dp)[:2],
+                           oracle.generate_displaced_pole_grid(ni, nj, lon0, lat0, lon_dp, r_dp)[:2], ("x", "y")):
+            assert_bits(g, r, what + " mesh " + n)
+    for trial in range(10):
+        order = int(rng.integers(2, 6))
+        ni = int(rng.choice([8, 31, 32, 33, 96, 130]))
+        nj = int(rng.integers(2, 16))
+        lat0 = float(rng.choice([40.0, 46.0, 64.05895973, 85.0])) + float(rng.uniform(-1, 1)) * (trial % 2)
+        lon_bp = float(rng.uniform(-360, 360))
+        rp = G.bipolar_rp(lat0)
+        assert rp == oracle.bipolar_rp(lat0)
+        what = "bp trial %d: order %d ni %d nj %d lat0 %r lon_bp %r" % (trial, order, ni, nj, lat0, lon_bp)
+        for g, r, n in zip(G.bipolar_cap_metrics_quad_fast(order, ni, nj, lat0, lon_bp, rp),
+                           oracle.bipolar_cap_metrics_quad_fast(order, ni, nj, lat0, lon_bp, rp), ("dxq", "dyq", "daq")):
+            assert_bits(g, r, what + " " + n)
+        for g, r, n in zip(G.generate_bipolar_cap_mesh(ni, nj, lat0, lon_bp),
+                           oracle.generate_bipolar_cap_mesh(ni, nj, lat0, lon_bp), ("lams", "phis", "h_i_inv", "h_j_inv")):
+            assert_bits(g, r, what + " mesh " + n)
+
+
 def test_monotonic_bounding_adversarial(G, oracle):
     """Random jumps exercise every branch of the 2-state scan, including chains where the shift state flips often,
     rows longer than one scan tile and values sitting on the 100-degree threshold."""
