@@ -1256,8 +1256,17 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
                                                                  const int* __restrict__ tok) {
   constexpr int NM = 4 * NV, NT = 1 + 2 * NV, TW = THREADS - 1, kWarps = THREADS / 32;
   constexpr unsigned kMask = (1u << NM) - 1u;
+#ifndef OGG_NO_IDX32
+  // one array for both parks (one base address + immediate offsets) and 32-bit item / column numbers (the host refuses
+  // launches of 2**31 items or more): at 48 registers the compiler re-derives the table and shared-memory addresses
+  // for every vertex instead of keeping them, and a 64-bit derivation is twice the instructions
+  __shared__ double parkS[2 * NM][THREADS];
+  double (*const lamS)[THREADS] = parkS;
+  double (*const phiS)[THREADS] = parkS + NM;
+#else
   __shared__ double lamS[NM][THREADS];
   __shared__ double phiS[NM][THREADS];
+#endif
   __shared__ unsigned shw[2 * kWarps];
   __shared__ unsigned s_state;
   const DpConst K = dp_load(cst);
@@ -1269,17 +1278,30 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
   {
     if (threadIdx.x == 0) s_item = (i64)atomicAdd(desc + nitem, 1ull);   // the ticket counter follows the descriptors
     __syncthreads();
+#ifndef OGG_NO_IDX32
+    const unsigned item = (unsigned)s_item;
+    const unsigned t = item / (unsigned)nrow, r = item - t * (unsigned)nrow;
+    const int c = (int)(t * (unsigned)TW) + (int)threadIdx.x - 1;
+    const bool virt = c < 0;
+    const bool valid = !virt && c < (int)ncol;
+#else
     const i64 item = s_item;
     const i64 t = item / nrow, r = item - t * nrow;
     const i64 c = t * TW + (i64)threadIdx.x - 1;
     const bool virt = c < 0;
     const bool valid = !virt && c < ncol;
+#endif
     {
       // every thread projects (the few past the last column redo column 0 and drop the result): no per-thread
       // predicate around the loop, so its constants stay in uniform registers (-3 %)
-      const Cx* cc = ct + (valid ? c : 0) * NT;
-      const double* rr = rt + r * NT;
-      mf.base = (tok[valid ? c : 0] & tok[ncol + r]) != 0 && (!SMALLAT || K.r_joint > 0.0);   // dp_vertex_fast's preconditions
+      const unsigned cidx = valid ? (unsigned)c : 0u;
+      const Cx* cc = ct + (size_t)cidx * NT;
+      const double* rr = rt + (size_t)r * NT;
+      mf.base = (tok[cidx] & tok[ncol + r]) != 0 && (!SMALLAT || K.r_joint > 0.0);   // dp_vertex_fast's preconditions
+      // A vertex whose guard flag fails (a zero / non-finite / extreme operand: the pole row, an axis crossing) is
+      // redone with the compiler's operators AFTER the loop: a call inside it, even one never taken, makes the compiler
+      // re-load the ~20 coefficients it keeps in uniform registers after every vertex (-80 LDCU per sample).
+      unsigned bad = 0u;
 #pragma unroll UNR
       for (int m = 0; m < NM; ++m) {
         const int lvl = m >> 2, kind = m & 3;
@@ -1288,12 +1310,28 @@ __global__ void __launch_bounds__(THREADS, MINB) k_dp_hsamples(const Cx* __restr
         double l, p;
         mf.reset();
         dp_vertex_fast<SMALLAT>(mf, rv, ep, K, l, p);
-        if (!mf.ok()) {   // a zero / non-finite / extreme operand somewhere (the pole row, an axis crossing)
+#ifdef OGG_DP_REDO_INLOOP
+        if (!mf.ok()) {
           const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
           l = o.l; p = o.p;
         }
+#else
+        if (!mf.ok()) bad |= 1u << m;
+#endif
         lamS[m][threadIdx.x] = l;
         phiS[m][threadIdx.x] = p;
+      }
+      if (bad) {
+#pragma unroll 1
+        for (int m = 0; m < NM; ++m) {
+          if (!((bad >> m) & 1u)) continue;
+          const int lvl = m >> 2, kind = m & 3;
+          const double rv = rr[kind < 2 ? 0 : 2 * lvl + kind - 1];
+          const Cx ep = cc[kind < 2 ? 2 * lvl + kind + 1 : 0];
+          const LamPhi o = dp_vertex_ieee(rv, ep.re, ep.im, K.r_joint, K.z0.re, K.z0.im);
+          lamS[m][threadIdx.x] = o.l;
+          phiS[m][threadIdx.x] = o.p;
+        }
       }
     }
     if (!valid) {
@@ -2134,9 +2172,10 @@ __global__ void __launch_bounds__(256) k_dp_quad_setup(QuadNodes q, int order, i
   }
   for (i64 e = t; e < ndesc; e += (i64)gridDim.x * blockDim.x) desc[e] = 0ull;
 }
-#ifndef OGG_DP_MINB   // tuning knobs of the order-4 instantiation (the one main() uses)
-#define OGG_DP_MINB 5
-#endif
+#ifndef OGG_DP_MINB   // tuning knobs of the order-4 instantiation (the one main() uses).  4 CTAs/SM = 64 registers: the
+#define OGG_DP_MINB 4 // kernel is issue-bound (2F + O), so the registers buy more (fewer re-derived addresses
+#endif                // and re-loaded coefficients) than a fifth resident CTA: 0.4060 -> 0.3938 ms
+
 #ifndef OGG_DP_UNR
 #define OGG_DP_UNR 4
 #endif
