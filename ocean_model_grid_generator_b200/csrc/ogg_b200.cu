@@ -1194,8 +1194,10 @@ __device__ __noinline__ double haversine_ol(double lam0, double phi0, double lam
   const double2 ra = m.pair(T_RED0), rb = m.pair(T_RED1);
   const double l0 = lam0 * kPi180, p0 = phi0 * kPi180, l1 = lam1 * kPi180, p1 = phi1 * kPi180;
   const double x1 = 0.5 * (p1 - p0), x2 = 0.5 * (l1 - l0);
-  const double k1 = rint(x1 * ra.x), k2 = rint(x2 * ra.x), k3 = rint(p0 * ra.x), k4 = rint(p1 * ra.x);
-  const int i1 = static_cast<int>(static_cast<long long>(k1)), i2 = static_cast<int>(static_cast<long long>(k2));
+  const double k3 = rint(p0 * ra.x), k4 = rint(p1 * ra.x);
+  // the half-differences' quadrant numbers are only tested for zero: converted with round-to-nearest-even (= rint) in one
+  // instruction, as 64-bit integers so that a huge quotient cannot alias to 0
+  const int i1 = (__double2ll_rn(x1 * ra.x) == 0LL) ? 0 : 1, i2 = (__double2ll_rn(x2 * ra.x) == 0LL) ? 0 : 1;
   const int i3 = static_cast<int>(static_cast<long long>(k3)), i4 = static_cast<int>(static_cast<long long>(k4));
   double d;
   if ((i1 | i2) == 0 && (i3 & i4 & 1) != 0) {
