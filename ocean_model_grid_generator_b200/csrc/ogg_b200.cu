@@ -792,15 +792,16 @@ __global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const
   extern __shared__ double smem[];
   double* sx = smem;
   double* sy = smem + SR * SCP;
-  const i64 gr0 = (i64)blockIdx.y * TR * (N - 1), gc0 = (i64)blockIdx.x * TC * (N - 1);
-  const i64 nreg = (N - 1) * ncr + 1;  // regular unique rows of this slab
+  // sample row / column numbers fit 31 bits (the host checks): 32-bit arithmetic in the per-sample bounds and addresses
+  const int gr0 = (int)blockIdx.y * TR * (N - 1), gc0 = (int)blockIdx.x * TC * (N - 1);
+  const int nreg = (N - 1) * (int)ncr + 1;  // regular unique rows of this slab
   // cached divisors pi/180, nx, ny (all moderate: nx, ny >= 1) with their refined reciprocals, stored by k_bp_quad_tables
   MathFast mf(divs);
   mf.base = bp_rp_ok(rp);
   const MathFast::Divisor dnx = MathFast::load_divisor(divs + 2), dny = MathFast::load_divisor(divs + 4);
   // one sample: scaled h_i_inv, h_j_inv of unique row r / column c of this tile -> shared memory
-  auto sample = [&](int r, int c, const BpCol& C, bool col_ok) {
-    const i64 gr = gr0 + r;
+  auto sample = [&](int r, int cpos, const BpCol& C, bool col_ok) {   // cpos: the column's part of the smem position
+    const int gr = gr0 + r;
     double a = 0.0, b = 0.0;
     if (col_ok && gr < nreg) {
       const BpRow R = rt[gr];
@@ -817,10 +818,11 @@ __global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const
         a = o.a; b = o.b;
       }
     }
-    const int pos = r * SCP + (c % (N - 1)) * (TC + 1) + c / (N - 1);
+    const int pos = r * SCP + cpos;
     sx[pos] = a;
     sy[pos] = b;
   };
+  auto col_pos = [](int c) { return (c % (N - 1)) * (TC + 1) + c / (N - 1); };
   // a thread keeps ONE sample column (its column-table entry stays in registers, a warp covers 32 consecutive
   // columns of one row, whose row-table entry is a broadcast load) and walks down the rows, G row-interleaved groups
   // of SC-1 threads; the tile's last column goes to the first SR threads of the last group, which has the fewest rows.
@@ -828,20 +830,21 @@ __global__ void __launch_bounds__(kBpThreads, OGG_BP_MINB) k_bp_quad_fused(const
   static_assert(G >= 1 && SR <= CM, "a row of sample columns per thread group");
   const int grp = threadIdx.x / CM, cm = threadIdx.x - grp * CM;
   if (grp < G) {
-    const bool col_ok = gc0 + cm < nuc;
+    const bool col_ok = gc0 + cm < (int)nuc;
     BpCol C{0.0, 0.0, 0.0};
     if (col_ok) C = ct[gc0 + cm];
     const bool extra = grp == G - 1 && cm < SR;
+    int cpos = col_pos(cm);
     for (int r = grp;; r += G) {        // one call site: the sample code is large
-      int rr = r, cc = cm;
+      int rr = r;
       bool ok = col_ok;
       const bool tail = r >= SR;
       if (tail) {
         if (!extra) break;
-        rr = cm; cc = CM; ok = gc0 + CM < nuc;
+        rr = cm; cpos = col_pos(CM); ok = gc0 + CM < (int)nuc;
         if (ok) C = ct[gc0 + CM];
       }
-      sample(rr, cc, C, ok);
+      sample(rr, cpos, C, ok);
       if (tail) break;
     }
   }
@@ -1695,6 +1698,7 @@ static int launch_bp_quad_fused(const BpCol* ct, const BpRow* rt, const double* 
     OGG_CUDA(cudaFuncSetAttribute(k_bp_quad_fused<N, TR, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured[dev] = true;
   }
+  if (nuc > 0x7fff0000LL || (N - 1) * ncr > 0x7fff0000LL) return OGG_ERR_ARG;   // the kernel's 32-bit sample numbers
   const dim3 g(cdiv_u(nx, TC), cdiv_u(ncr, TR));
   launch_begin(KID_BP_QUAD, st);
   k_bp_quad_fused<N, TR, TC><<<g, kBpThreads, smem, st>>>(ct, rt, divs, nuc, ncr, nx, ny, lat0_bp, lon_bp, rp, Re, dxq, dyq, daq);
