@@ -34,6 +34,7 @@ extern "C" {
 #define OGG_ERR_ORDER_NOT_CODED (-2) /* reference: Exception("order not coded")    OGG:547,562     */
 #define OGG_ERR_SHAPE (-3)           /* reference: shape-mismatch exceptions        OGG:229,722     */
 #define OGG_ERR_ARG (-4)
+#define OGG_ERR_TOO_LARGE (-5)       /* request exceeds the fixed work array of a *_noalloc entry point (see below) */
 #define OGG_ERR_CUDA (-1000)
 
 /* flags of ogg_band_fill_metrics */
@@ -135,6 +136,35 @@ int ogg_dp_mesh(const double* i, int64_t nil, const double* j, int64_t njl, int6
  * index vectors np.arange(Ni+1), np.arange(j0, j1) are formed on the device.  lams, phis [j1-j0][Ni+1]. */
 int ogg_dp_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0, double lat0, double lam_pole,
                     double r_pole, double* lams, double* phis, void* stream);
+/* ogg_dp_cap_mesh for callers that must not allocate device memory.  No counterpart in the reference (numpy allocates
+ * as it pleases); same arguments, same outputs, bit for bit, as ogg_dp_cap_mesh above.
+ *
+ * Who needs it.  ogg_dp_cap_mesh draws its work tables from a stream-ordered memory pool the library owns.  Three kinds of
+ * caller cannot live with that: a model component with a fixed device-memory budget planned at start-up (a pool that
+ * grows behind its back is memory it has not accounted for); a thread in a region where entering the CUDA allocator is
+ * off limits because the allocator takes a driver-wide lock and its first use may synchronise the whole device; and a
+ * process whose device memory belongs to another runtime (an MPI, OpenACC or Fortran host) that forbids foreign
+ * allocations.  This entry point calls no cudaMalloc / cudaMallocAsync / cudaFree and no library routine that does; the
+ * caller still supplies lams and phis.
+ *
+ * Where the work tables live.  In one fixed array of OGG_NOALLOC_SCRATCH_DOUBLES doubles (2 MiB) that is part of the
+ * library's device image: every GPU on which the library is used holds it until the process exits.  The limit this
+ * puts on a request is   32 + 2 * (Ni + 1) + (j1 - j0)  <=  OGG_NOALLOC_SCRATCH_DOUBLES   (e.g. Ni = 86400, the
+ * 1/120-degree supergrid, with up to 89310 mesh rows per call; taller caps are done in row ranges, which is what
+ * j0, j1 are for).  A larger request returns OGG_ERR_TOO_LARGE and launches nothing.
+ *
+ * First call on a device.  It looks up the device address of the array (cudaGetSymbolAddress, which may load the
+ * library's device code onto that GPU); later calls on that device reuse the address.  Make that first call, on every
+ * device you use, during set-up and before you begin capturing any stream.
+ *
+ * Sharing.  All calls on one device use the same array.  Each call rewrites every slot it reads before reading it, so
+ * nothing has to be cleared between calls and one call never sees another's leftovers -- provided they do not run at
+ * the same time: two calls whose kernels can overlap on the GPU (different streams without an event between them,
+ * or two host threads) overwrite each other's tables and both results are garbage.  Order them on one stream, or with
+ * events. */
+#define OGG_NOALLOC_SCRATCH_DOUBLES 262144
+int ogg_dp_cap_mesh_noalloc(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0, double lat0, double lam_pole,
+                            double r_pole, double* lams, double* phis, void* stream);
 /* great_arc_distance (OGG:522-532) -> out[njl][nil] */
 int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl,
                            int64_t nil, int64_t nx, int64_t ny, double lon0, double lat0, double lon_dp,

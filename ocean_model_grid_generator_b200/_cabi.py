@@ -52,6 +52,7 @@ SIGNATURES = {
     "ogg_monotonic_bounding": [_dp, _i64, _i64, _d, _vp],
     "ogg_dp_mesh": [_dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
     "ogg_dp_cap_mesh": [_i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
+    "ogg_dp_cap_mesh_noalloc": [_i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _dp, _vp],
     "ogg_great_arc_distance": [_dp, _dp, _dp, _dp, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _dp, _vp],
     "ogg_numerical_h": [_int, _dp, _i64, _dp, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _vp],
     "ogg_dp_metrics_quad": [_int, _i64, _i64, _i64, _i64, _d, _d, _d, _d, _d, _int, _dp, _dp, _dp, _vp],
@@ -72,7 +73,9 @@ OGG_ERR_UNCODED_ORDER = -1
 OGG_ERR_ORDER_NOT_CODED = -2
 OGG_ERR_SHAPE = -3
 OGG_ERR_ARG = -4
+OGG_ERR_TOO_LARGE = -5
 OGG_ERR_CUDA = -1000
+OGG_NOALLOC_SCRATCH_DOUBLES = 262144   # include/ogg_b200.h
 
 
 class OggError(RuntimeError):
@@ -118,6 +121,10 @@ def check(rc, what=""):
         raise Exception("Input arrays do not have the same shape!")
     if rc == OGG_ERR_ARG:
         raise OggError("invalid argument to %s" % what)
+    if rc == OGG_ERR_TOO_LARGE:
+        raise OggError("%s: the request does not fit the library's fixed %d-double work array (no-allocation entry "
+                       "points never grow it); split the rows into smaller ranges or use the allocating entry point"
+                       % (what, OGG_NOALLOC_SCRATCH_DOUBLES))
     if rc <= OGG_ERR_CUDA:
         raise OggError("CUDA error %d in %s" % (OGG_ERR_CUDA - rc, what))
     raise OggError("status %d from %s" % (rc, what))

@@ -2111,6 +2111,91 @@ int ogg_dp_cap_mesh(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0,
   return dp_mesh_dev(nullptr, 0, Ni + 1, 0.0, nullptr, j0, j1 - j0, 0.0, Ni, Nj, lon0, lat0, cst, lams, phis, st);
 }
 
+}  // extern "C"
+
+namespace ogg {
+// ------------------------------------------------------------------------------------------------
+// ogg_dp_cap_mesh_noalloc: the displaced-pole cap mesh for hosts that must not allocate.
+//
+// Who that is: an ocean model's I/O or coupler layer that hands this library two output arrays from its own arena and
+// has a fixed device-memory budget (every byte of HBM is accounted for at start-up, so a library that grows a memory
+// pool behind its back breaks the budget); a thread that is inside a region where the CUDA allocator may not be entered
+// (it takes a driver-wide lock, and a first stream-ordered allocation may synchronise the device); a process whose
+// device memory is handed out by another runtime (an MPI / OpenACC / Fortran host) that forbids foreign cudaMalloc calls.
+// ogg_dp_cap_mesh takes its three work tables (the column table, the row table, a handful of constants) from the
+// library's cudaMallocFromPoolAsync pool; this variant keeps them in the array below instead, which is part of the
+// loaded module: every device that loads libogg_b200.so holds these 2 MiB from the first use of the library on that
+// device until the process exits, whether or not this entry point is ever called.
+//
+// The name g_noalloc_scratch is only meaningful in device code.  Host code gets the array's device address with
+// cudaGetSymbolAddress, once per device and with that device current (noalloc_scratch below), and hands that pointer to
+// the kernels; passing the bare name from the host would hand them a host-side shadow address.
+// ------------------------------------------------------------------------------------------------
+constexpr i64 kNoAllocDoubles = OGG_NOALLOC_SCRATCH_DOUBLES;   // include/ogg_b200.h: 262144 doubles = 2 MiB
+constexpr i64 kNoAllocHeader = 32;                             // constants: [0,3) r_joint, z0; [4,6) pi/180 pair; [8,20) x_0 slots
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocDoubles];
+
+// Device address of g_noalloc_scratch on the CURRENT device (nullptr + *err on failure).  The first call on a device
+// asks the runtime for the address (which also makes sure the module is loaded there); later calls read the cached value.
+static double* noalloc_scratch(cudaError_t* err) {
+  static double* ptrs[kMaxDevices] = {nullptr};
+  static std::mutex mu;
+  *err = cudaSuccess;
+  int dev = -1;
+  *err = cudaGetDevice(&dev);
+  if (*err != cudaSuccess) return nullptr;
+  if (dev < 0 || dev >= kMaxDevices) { *err = cudaErrorInvalidDevice; return nullptr; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    *err = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (*err != cudaSuccess) return nullptr;
+    ptrs[dev] = static_cast<double*>(p);
+  }
+  return ptrs[dev];
+}
+}  // namespace ogg
+
+extern "C" {
+
+int ogg_dp_cap_mesh_noalloc(int64_t Ni, int64_t Nj, int64_t j0, int64_t j1, double lon0, double lat0, double lam_pole,
+                            double r_pole, double* lams, double* phis, void* stream) {
+  if (Ni < 1 || Nj < 1 || j0 < 0 || j1 > Nj + 1 || j0 >= j1 || !lams || !phis) return OGG_ERR_ARG;
+  const i64 nil = Ni + 1, njl = j1 - j0;
+  // the whole request must fit the fixed array: header + one complex number per mesh column + one real per mesh row
+  if (nil > kNoAllocDoubles || njl > kNoAllocDoubles || kNoAllocHeader + 2 * nil + njl > kNoAllocDoubles)
+    return OGG_ERR_TOO_LARGE;
+  cudaError_t err;
+  double* ws = noalloc_scratch(&err);
+  if (!ws) return OGG_ERR_CUDA - (int)err;
+  cudaStream_t st = S(stream);
+  // Every slot read below is written earlier in this same call, in stream order: nothing has to start at zero, and
+  // whatever the previous call left behind is never looked at.
+  double* cst = ws;            // r_joint, Re z_0, Im z_0
+  double* pi180 = ws + 4;      // pi/180 and its refined reciprocal
+  double* x0 = ws + 8;         // k_dp_x0<1> writes 4 slots; slot 2 is the unshifted x_0 = lon_grid[0,0]
+  Cx* ct = reinterpret_cast<Cx*>(ws + kNoAllocHeader);
+  double* rt = ws + kNoAllocHeader + 2 * nil;
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_constants), (1, 32), (st), lat0, lam_pole, r_pole, cst);
+  OGG_LAUNCH_CHECK();
+  OGG_LAUNCH(KID_DP_SETUP, (k_store_pi180), (1, 32), (st), pi180);
+  OGG_LAUNCH_CHECK();
+  OGG_LAUNCH(KID_DP_SETUP, (k_dp_x0<1>), (1, 32), (st), (const double*)nullptr, 0.0, 0.0, Ni, lon0, x0);
+  OGG_LAUNCH_CHECK();
+  const i64 m = nil > njl ? nil : njl;
+  OGG_LAUNCH(KID_DP_TABLES, (k_dp_tables), (cdiv_u(m, 256), 256), (st), (const double*)nullptr, (i64)0, nil, 0.0,
+             (const double*)nullptr, (i64)j0, njl, 0.0, (i64)Ni, (i64)Nj, lon0, lat0, (const double*)cst, ct, rt);
+  OGG_LAUNCH_CHECK();
+  OGG_LAUNCH(KID_DP_RAW, (k_dp_lattice_raw), (lattice_grid(nil, njl, 256), 256), (st), (const Cx*)ct, (const double*)rt,
+             njl, nil, (const double*)cst, lams, phis, (const double*)pi180);
+  OGG_LAUNCH_CHECK();
+  const i64 cap = (i64)num_sms() * 8;
+  OGG_LAUNCH(KID_MONOTONIC, (k_monotonic), ((unsigned)(njl < cap ? njl : cap), kScanThreads), (st), lams, njl, nil, 0.0,
+             (const double*)(x0 + 2));
+  OGG_LAUNCH_CHECK();
+  return OGG_OK;
+}
+
 int ogg_great_arc_distance(const double* j0, const double* i0, const double* j1, const double* i1, int64_t njl, int64_t nil,
                            int64_t nx, int64_t ny, double lon0, double lat0, double lon_dp, double r_dp, double* out,
                            void* stream) {
