@@ -87,6 +87,75 @@ def test_halo_exchange_and_allreduce_gloo(world, nyp, nxp):
     assert got == {r: True for r in range(world)}
 
 
+def _worker_validate(rank, world, port, q):
+    """exchange_halo's cross-rank check: done on the first call for a (group, nxp) only, on every call when asked, and
+    a mesh without a row to send makes every rank raise together when it is done."""
+    for p in (ROOT, os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ocean_model_grid_generator_b200 import slabs
+        from util import bits_equal
+        calls = []
+        real = dist.all_reduce
+
+        def counting(*a, **k):
+            calls.append(1)
+            return real(*a, **k)
+        dist.all_reduce = counting
+        ok = True
+        x, y = _mesh(9, 12)
+        v0, v1 = slabs.vertex_rows(8, rank, world)
+        xs, ys = torch.from_numpy(x[v0:v1].copy()), torch.from_numpy(y[v0:v1].copy())
+        for rep in range(3):
+            halo = slabs.exchange_halo(xs, ys)
+            if rank < world - 1:
+                ok &= bits_equal(halo[0].numpy(), x[v1]) and bits_equal(halo[1].numpy(), y[v1])
+        ok &= len(calls) == 1                      # "once": only the first of the three calls validated
+        slabs.exchange_halo(xs, ys, validate="always")
+        slabs.exchange_halo(xs, ys, validate="never")
+        ok &= len(calls) == 2
+        # a new number of columns is a new combination: checked again, and the last rank's empty slab is caught by all
+        x2, y2 = _mesh(9, 7)
+        xe = torch.from_numpy(x2[v0:v1].copy()) if rank < world - 1 else torch.empty((0, 7), dtype=torch.float64)
+        ye = torch.from_numpy(y2[v0:v1].copy()) if rank < world - 1 else torch.empty((0, 7), dtype=torch.float64)
+        try:
+            slabs.exchange_halo(xe, ye)
+            ok = False
+        except Exception as e:
+            ok &= "no mesh row" in str(e)
+        ok &= len(calls) == 3
+        # what a rank can see by itself is checked on every call, validated combination or not
+        try:
+            slabs.exchange_halo(xs, ys[:, :-1], validate="never")
+            ok = False
+        except Exception as e:
+            ok &= "same shape" in str(e)
+        dist.all_reduce = real
+        dist.barrier()
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_halo_validation_modes_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_validate, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    got = dict(q.get(timeout=5) for _ in range(world))
+    assert got == {r: True for r in range(world)}
+
+
 def test_slab_bounds_cover_and_balance():
     from ocean_model_grid_generator_b200 import slabs
     for n in (0, 1, 7, 8, 143, 1400):
