@@ -98,13 +98,19 @@ def load(build_if_missing=True):
             raise OggError("libogg_b200.so is missing (%s); run __graft_entry__.build()" % path)
         _build.build()
     lib = ctypes.CDLL(path)
+    skipped = []
     for name, argtypes in SIGNATURES.items():
         if os.environ.get("OGG_B200_LIB") and not hasattr(lib, name):
-            continue             # developer A/B against an older build of the same sources (tools/kbench.py)
+            skipped.append(name)  # developer A/B against an older build of the same sources (tools/kbench.py)
+            continue
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.argtypes = argtypes
         fn.restype = (ctypes.c_char_p if name in ("ogg_version", "ogg_timing_name")
                       else ctypes.c_longlong if name == "ogg_launch_count" else _int)
+    if skipped:
+        import warnings
+        warnings.warn("OGG_B200_LIB=%s does not export %s; calling any of them will fail with AttributeError"
+                      % (path, ", ".join(skipped)))
     _LIB = lib
     return lib
 

@@ -267,9 +267,10 @@ __global__ void __launch_bounds__(256) k_band_tables(const double* __restrict__ 
   }
 }
 
-// One launch fills every band of a step: blockIdx.y runs over the row tiles of all bands, one thread per column, R rows
-// per CTA (host-chosen so that the grid is close to a whole number of waves of resident CTAs -- at -r 4 the fixed
-// 8-row tiles of round 1 left the second wave 78 % full).  A thread keeps the column-only factors in registers; the
+// One launch fills every band of a step: blockIdx.y runs over the row tiles of all bands, one thread per column,
+// kBandRows (a compile-time 8) rows per CTA.  Choosing the rows per CTA on the host so that the grid comes close to a
+// whole number of waves was tried with a run-time loop bound and with 4 / 12 / 16 compiled rows and measured slower
+// than the fixed 8 rows x 5 CTAs/SM (DESIGN.md "tried and rejected"); it is not what ships.  A thread keeps the column-only factors in registers; the
 // row-only factors are uniform loads.  Stores are plain 8-byte stores, a warp writing 256 contiguous bytes per array and
 // row: 16-byte pair stores (which need a per-row alignment shift because the row length nxp is odd) and column strips
 // with a one-wave persistent grid were both measured slower (DESIGN.md "tried and rejected").
@@ -281,7 +282,7 @@ struct BandDesc {
   int metrics;
 };
 constexpr int kMaxBands = 4;
-struct BandBatch { BandDesc b[kMaxBands]; int n; i64 rows_per_tile; double Re, Re2; };
+struct BandBatch { BandDesc b[kMaxBands]; int n; double Re, Re2; };
 
 OGG_DI double band_angle(double xdv, double cyj, double dyc, double ang_pos, double ang_neg) {
   // angle_x on a band (:725-728): y[ia]-y[ib] = phi-phi = +0, so p_atan2 takes its ay == 0 branch: +0 for a
@@ -453,9 +454,16 @@ __global__ void __launch_bounds__(256) k_angle(const double* __restrict__ x, con
       const double* xr = x + j * nxp;
       const double* yr = y + j * nxp;
       const double dy = yr[ia] - yr[ib], dx = xr[ia] - xr[ib], yc = yr[i];
-      mf.reset();
-      double a = mf.div_pi180(p_atan2(mf, dy, dx * p_cos(mf, yc * kPi180)));
-      if (!mf.ok()) a = angle_ieee(dy, dx, yc);
+      double a;
+      if (dy == 0.0 || dx == 0.0) {
+        // a grid line along a parallel or a meridian (every vertex of a regular or Mercator mesh): the fast path's
+        // guard is known to fail, so do not evaluate it first
+        a = angle_ieee(dy, dx, yc);
+      } else {
+        mf.reset();
+        a = mf.div_pi180(p_atan2(mf, dy, dx * p_cos(mf, yc * kPi180)));
+        if (!mf.ok()) a = angle_ieee(dy, dx, yc);
+      }
       OGG_OUT_ST(angle[j * nxp + i], a);
     }
     return;
@@ -1883,7 +1891,6 @@ int ogg_band_fill_metrics_batch(const ogg_band_t* bands, int nbands, double Re, 
   }
   const i64 ncb = (nxp_max + kBandThreads - 1) / kBandThreads;
   const i64 R = kBandRows;
-  B.rows_per_tile = R;
   i64 tiles = 0;
   for (int k = 0; k < nbands; ++k) { B.b[k].t_begin = tiles; tiles += (B.b[k].nyp + R - 1) / R; }
   if (tiles > 65535) return OGG_ERR_ARG;
@@ -2300,7 +2307,9 @@ template <int NV, int THREADS, int MINB, int UNR, bool SMALLAT = false>
 static int dp_hsamples_t(const Cx* ct, const double* rt, i64 nrow, i64 ncol, const double* x0v, const double* cst,
                          double reps, double* hx, double* hy, unsigned long long* desc, const int* tok, cudaStream_t st) {
   const i64 nitem = nrow * ((ncol + THREADS - 2) / (THREADS - 1));
-  if (nitem > 0x7fffffffLL) return OGG_ERR_ARG;
+  // the kernel numbers items, columns and tiles in 32 bits (t * TW, (int)ncol, (unsigned)nrow): bound each of them,
+  // not only their product (few rows of very many columns would pass the item count and wrap the column number)
+  if (nitem > 0x7fffffffLL || ncol > 0x7fff0000LL || nrow > 0x7fff0000LL) return OGG_ERR_ARG;
   launch_begin(KID_DP_HSAMPLES, st);
   k_dp_hsamples<NV, THREADS, MINB, UNR, SMALLAT><<<(unsigned)nitem, THREADS, 0, st>>>(ct, rt, nrow, ncol, x0v, cst, reps, hx, hy, desc, tok);
   launch_end(st);

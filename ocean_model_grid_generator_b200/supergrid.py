@@ -554,6 +554,15 @@ def run_main(args):
     if len(plan.pieces) < 2:
         raise Exception("nothing to stitch: the reference needs at least two adjoining sub-grids (OGG:1237-1247)")
     sg = build_supergrid(plan)               # one in-place build of the stitched grid; everything below reads it
+    # OGG_CHECK_LINES=0: leave out the CHECK_metrics lines.  They are the reference's self-check prints, not part of the
+    # file; for the displaced-pole cap they cost a second pass over the whole cap's quadrature (the rows inside the
+    # doughnut are never stored), and for sub-grids the stitched arrays cannot serve (a regular southern cap, a cut
+    # Southern Ocean) a stand-alone build next to the resident grid -- at 1/30 degree and finer that is most of the
+    # CLI's cap work and extra HBM a user may not have.
+    import os
+    check_lines = os.environ.get("OGG_CHECK_LINES", "1") != "0"
+    if not check_lines:
+        print("   self-check lines left out (OGG_CHECK_LINES=0)")
     # Per sub-grid, in main()'s order (Mercator, bipolar cap, Southern Ocean, southern cap): the CHECK_metrics line and,
     # with --write_subgrid_files, its own file.  A sub-grid's file holds its OWN closing vertex row (which the join
     # drops) and the rows main() had at that point -- Mercator / bipolar / Southern Ocean as generated (OGG:1020, 1074,
@@ -567,7 +576,8 @@ def run_main(args):
         if args["write_subgrid_files"]:
             standalone = build_piece_standalone(plan, file_piece)
         full_build = standalone if (standalone is not None and file_piece.row0 == 0) else None
-        check_line(plan, name, sg, full_build)
+        if check_lines:
+            check_line(plan, name, sg, full_build)
         if standalone is not None:
             a = standalone.arrays()
             ogg.write_nc(a["x"], a["y"], a["dx"], a["dy"], a["area"], a["angle_dx"], axis_units="degrees",

@@ -51,6 +51,10 @@ CONFIGS = {  # extras/Makefile:28-39 (file name / subgrid flags dropped; they do
     "res1.0_cutang": "-r 1.0 --r_dp 0.2 --south_cutoff_ang -80.4 --no_changing_meta",
     "res1.0_cutso": "-r 1.0 --r_dp 0.2 --south_cutoff_row 45 --no_changing_meta",
     "res0.5_cutang_regular": "-r 2 --south_cutoff_ang -81.1 --no_changing_meta",
+    # --ensure_nj_even on a default-flag grid, where it shortens the Mercator band (OGG:329-333) AND cuts the southern row
+    # of the doughnut-cut displaced-pole cap (OGG:1188-1194): pins oracle/supergrid_cpu.build_cpu(ensure_nj_even=True),
+    # the checker of the 1/30-degree slabs (BASELINE configs[3] is `-r 30 --r_dp 0.2 --ensure_nj_even`)
+    "res0.667_dp_even": "-r 1.5 --r_dp 0.2 --ensure_nj_even --no_changing_meta",
 }
 QUICK = ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp"]
 

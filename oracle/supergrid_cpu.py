@@ -21,13 +21,16 @@ def _bounds(ncells, rank, world):
     return c0, c0 + base + (1 if rank < rem else 0)
 
 
-def build_cpu(r, r_dp=0.0, south_cutoff_row=0, exfracdp=0.49, timings=None, slab=None):
+def build_cpu(r, r_dp=0.0, south_cutoff_row=0, exfracdp=0.49, timings=None, slab=None, ensure_nj_even=False):
+    """ensure_nj_even (the CLI flag, OGG:873): coded for what it changes on a default-flag integer-r grid -- the Mercator
+    row count (OGG:329-333) and the doughnut-cut displaced-pole cap (OGG:1188-1194).  The bipolar cap's 120*r rows are
+    even already (OGG:107); a Southern Ocean band or regular cap that the flag would shorten raises (not coded here)."""
     import time
     t0 = time.time()
     refineS, lon0, lenlon = 2, -300.0, 360
     Ni = int(r * refineS * lenlon)
     phi_s, phi_n = (-68.0, 65.0) if r == 2 else (-66.85954725, 64.05895973)
-    phiM = O.mercator_phi_1d(Ni, phi_s, phi_n, True, False)
+    phiM = O.mercator_phi_1d(Ni, phi_s, phi_n, True, bool(ensure_nj_even))
     lam1 = lon0 + np.arange(Ni + 1) * lenlon / float(Ni)
     rank, world = slab if slab is not None else (0, 1)
 
@@ -50,6 +53,8 @@ def build_cpu(r, r_dp=0.0, south_cutoff_row=0, exfracdp=0.49, timings=None, slab
     lenlat_SO = phiM[0] - lat0_SO
     Nj_SO = int(r * 55)
     phiSO = lat0_SO + np.arange(Nj_SO + 1) * lenlat_SO / float(Nj_SO)
+    if ensure_nj_even and (Nj_ncap % 2 != 0 or (Nj_SO + 1) % 2 == 0):
+        raise ValueError("ensure_nj_even would cut a bipolar / Southern Ocean row at r=%r: not coded in this test helper" % r)
     lat0_SC = phiSO[0]
     Nj_scap = int(r * 40) * 7 // 4
     # south cut (OGG:1270-1313) as row offsets into SC / SO
@@ -57,9 +62,13 @@ def build_cpu(r, r_dp=0.0, south_cutoff_row=0, exfracdp=0.49, timings=None, slab
     if r_dp == 0.0:
         Nj_scap = int((lat0_SC + 90.0) / (1.0 / r / refineS))
         phiSC = -90.0 + np.arange(Nj_scap + 1) * (90 + lat0_SO) / float(Nj_scap)
+        if ensure_nj_even and (Nj_scap + 1) % 2 == 0:
+            raise ValueError("ensure_nj_even would cut a row of the regular southern cap at r=%r: not coded here" % r)
     else:
         jmin = np.ceil(exfracdp * Nj_scap)
         sc_row0 = int(jmin + np.mod(jmin, 2))
+        if ensure_nj_even and (Nj_scap + 1 - sc_row0) % 2 == 0:                                        # OGG:1188-1194
+            sc_row0 += 1
     sc_rows = Nj_scap + 1 - sc_row0
     if south_cutoff_row > 0:
         jcut = south_cutoff_row - 1

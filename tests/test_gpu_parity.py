@@ -371,6 +371,26 @@ def test_band_fused_equals_general(G, oracle):
     assert_bits(D.to_host(o[5]), oracle.angle_x(x, y), "angle")
 
 
+def test_angle_x_zero_differences_take_the_ieee_branch(G, oracle):
+    """angle_x on meshes whose centred differences are exact zeros -- along a parallel (dy == 0), along a meridian
+    (dx == 0), both, and mixed with ordinary vertices inside one warp: k_angle sends those vertices straight to the IEEE
+    expression instead of through the fast path first; the results are the oracle's either way."""
+    rng = np.random.default_rng(11)
+    nyp, nxp = 37, 131
+    lam = -300.0 + np.arange(nxp) * 360.0 / (nxp - 1)
+    phi = np.linspace(-80.0, 80.0, nyp)
+    x, y = np.tile(lam, (nyp, 1)), np.tile(phi.reshape(-1, 1), (1, nxp))
+    assert_bits(G.angle_x(x, y), oracle.angle_x(x, y), "parallel")                  # dy == 0 everywhere
+    xm = np.tile(rng.uniform(-300, 60, (nyp, 1)), (1, nxp))                         # dx == 0 everywhere
+    ym = y + rng.uniform(-1, 1, (nyp, nxp))
+    assert_bits(G.angle_x(xm, ym), oracle.angle_x(xm, ym), "meridian")
+    assert_bits(G.angle_x(xm, y), oracle.angle_x(xm, y), "both zero")
+    mix = rng.random((nyp, nxp)) < 0.5                                               # per-vertex mixture
+    x2 = np.where(mix, x, x + rng.uniform(-0.3, 0.3, (nyp, nxp)))
+    y2 = np.where(mix, y, ym)
+    assert_bits(G.angle_x(x2, y2), oracle.angle_x(x2, y2), "mixed")
+
+
 def _band_outputs(D, nyp, nxp):
     return [D.empty(nyp, nxp), D.empty(nyp, nxp), D.empty(nyp, nxp - 1), D.empty(nyp - 1, nxp), D.empty(nyp - 1, nxp - 1), D.empty(nyp, nxp)]
 

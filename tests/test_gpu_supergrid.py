@@ -32,7 +32,7 @@ def _plan_args(a):
 # branches no extras/Makefile recipe reaches (OGG:1050-1057, 1123-1125, 1276-1279, 1296-1313)
 @pytest.mark.parametrize("name", ["res4.0", "res1.0", "res0.5", "res0.5_equenh", "readme_dp", "res1.0_dp", "res0.25",
                                   "res0.25_om5proto", "res0.25_full", "res0.125", "res1.0_bp", "res1.0_p125sc",
-                                  "res1.0_cutang", "res1.0_cutso", "res0.5_cutang_regular"])
+                                  "res1.0_cutang", "res1.0_cutso", "res0.5_cutang_regular", "res0.667_dp_even"])
 def test_config_matches_reference_hashes(SG, golden_configs, name, capsys):
     cfg = golden_configs[name]
     plan = SG.plan_supergrid(**_plan_args(_args(cfg["flags"])))
@@ -96,6 +96,22 @@ def test_cli_check_lines_match_reference(SG, golden_configs, name, tmp_path, cap
         assert len(gv) == len(wv), (label, gv, wv)
         for g, w in zip(gv, wv):
             assert abs(g - w) <= 2e-10 + 1e-9 * abs(w), (name, label, gv, wv)
+
+
+def test_cli_check_lines_opt_out(SG, golden_configs, tmp_path, capsys, monkeypatch):
+    """OGG_CHECK_LINES=0 leaves the self-check prints (and the second pass over the displaced-pole cap behind them) out;
+    the file is the same file."""
+    from ocean_model_grid_generator_b200 import ocean_grid_generator as G
+    cfg = golden_configs["res1.0_dp"]
+    G.cli(["-f", str(tmp_path / "with.nc"), "--no_changing_meta"] + cfg["flags"].split())
+    assert len(_check_values(capsys.readouterr().out.splitlines())) > 0
+    monkeypatch.setenv("OGG_CHECK_LINES", "0")
+    G.cli(["-f", str(tmp_path / "without.nc"), "--no_changing_meta"] + cfg["flags"].split())
+    out = capsys.readouterr().out
+    assert _check_values(out.splitlines()) == [] and "left out (OGG_CHECK_LINES=0)" in out
+    a, b = (tmp_path / "with.nc").read_bytes(), (tmp_path / "without.nc").read_bytes()
+    # the history attribute holds the command line (the file name differs); everything from the data section on is equal
+    assert len(a) == len(b) and a[-(len(a) // 2):] == b[-(len(b) // 2):]
 
 
 def test_write_nc_device_path_equals_host_path(SG, tmp_path):
@@ -340,6 +356,42 @@ def test_eighth_degree_equals_cpu_oracle(SG, oracle, r):
         assert_bits(got[k], ref[k], "r=%d %s" % (r, k))
     tot = ref["area"].sum()
     assert abs(got["area"].sum() - tot) <= 1e-12 * tot
+
+
+# Row-slabs of the large grids against the CPU oracle.  slab = (k, V): rank k's share of every sub-grid's cell rows when the
+# grid is split V ways -- the same split (slabs.slab_bounds) on both sides.  The slab sizes keep the oracle's host time to
+# seconds: 1/V of a grid of P points at ~5e6 points/s.  k = 0 holds every sub-grid's southern edge (the doughnut edge of the
+# displaced-pole cap, the first Mercator row); the last k holds every closing row (the bipolar pole row, dx of the top
+# row); a middle k has neither.
+BIG_SLABS = [
+    (12, "", 8, 0), (12, "", 8, 3), (12, "", 8, 7),                       # N=8 weak-scaling grid (6725 x 8641), whole in 8 slabs
+    (30, "--ensure_nj_even", 32, 0), (30, "--ensure_nj_even", 32, 13), (30, "--ensure_nj_even", 32, 31),   # BASELINE configs[3]
+    (120, "", 512, 0), (120, "", 512, 255), (120, "", 512, 511),          # BASELINE configs[4]: Ni = 86400, 5.8e9 points
+]
+
+
+@pytest.mark.parametrize("r,extra,V,k", BIG_SLABS)
+def test_large_grid_slabs_equal_cpu_oracle(SG, oracle, r, extra, V, k):
+    """1/12, 1/30 and 1/120 degree (BASELINE configs[3] and [4], and the 8-GPU weak grid): a row-slab of the stitched
+    grid, all six arrays, bit for bit against the CPU oracle's evaluation of the same slab.  These are the sizes at which
+    the 32-bit item / column / sample numbers of the cap kernels, (i*360)/Ni at Ni = 21600 / 86400 and the chunked
+    quadrature are exercised (OGG:136-188, 565-601, 1316-1365)."""
+    import supergrid_cpu
+    import torch
+    plan = SG.plan_supergrid(**_plan_args(_args(("-r %d --r_dp 0.2 " % r) + extra)))
+    assert plan.Ni == 720 * r
+    sg = SG.Supergrid(plan, k, V).build()
+    got = sg.to_host()
+    del sg
+    torch.cuda.empty_cache()
+    ref = supergrid_cpu.build_cpu(r, r_dp=0.2, slab=(k, V), ensure_nj_even=bool(extra))
+    # the oracle's slab carries its top piece's closing vertex row, which belongs to the next slab (Supergrid.arrays()
+    # holds it on the last slab only)
+    n = ref["area"].shape[0] + (1 if k == V - 1 else 0)
+    assert n > 1
+    for name in NAMES:
+        want = ref[name][:n] if name in ("x", "y", "dx", "angle_dx") else ref[name]
+        assert_bits(got[name], want, "r=%d slab %d/%d %s" % (r, k, V, name))
 
 
 @pytest.mark.parametrize("rank,world", [(0, 1), (1, 3), (2, 3)])

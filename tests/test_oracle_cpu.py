@@ -188,7 +188,9 @@ def test_product_never_imports_oracle():
                                      ("res1.0_dp", dict(r=1.0, r_dp=0.2, south_cutoff_row=2)), ("res0.5", dict(r=2)),
                                      ("res1.0_cutso", dict(r=1.0, r_dp=0.2, south_cutoff_row=45)),
                                      # the benchmark's headline grid (BASELINE.json configs[1]) and bench.py's CPU arm
-                                     ("res0.25_full", dict(r=4, r_dp=0.2))])
+                                     ("res0.25_full", dict(r=4, r_dp=0.2)),
+                                     # --ensure_nj_even where it shortens the Mercator band and the cut displaced-pole cap
+                                     ("res0.667_dp_even", dict(r=1.5, r_dp=0.2, ensure_nj_even=True))])
 def test_oracle_supergrid_matches_reference_hashes(oracle, golden_configs, name, kw):
     import supergrid_cpu
     from util import sha
