@@ -191,7 +191,44 @@ def cpu_pass(r, r_dp, world=1):
     t0 = time.time()
     out = supergrid_cpu.build_cpu(r, r_dp=r_dp, slab=(0, world) if world > 1 else None)
     dt = time.time() - t0
+    _LAST_CPU_PASS[0] = out
     return out["x"].size / dt, dt, out["x"].shape
+
+
+_LAST_CPU_PASS = [None]
+
+
+FIELDS = ("x", "y", "dx", "dy", "area", "angle_dx")
+
+
+def host_checksums(arrays):
+    """The six per-array checksums ogg_checksum_accumulate computes on the device (sum over elements of the splitmix64
+    finaliser of the element's bit pattern, mod 2**64), computed with numpy integers on host arrays."""
+    import numpy as np
+    out = []
+    for k in FIELDS:
+        z = np.ascontiguousarray(arrays[k], dtype=np.float64).reshape(-1).view(np.uint64).copy()
+        z += np.uint64(0x9e3779b97f4a7c15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xbf58476d1ce4e5b9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94d049bb133111eb)
+        z ^= z >> np.uint64(31)
+        out.append("%016x" % int(z.sum(dtype=np.uint64)))
+    return out
+
+
+def own_rows(arrays, k, V):
+    """A slab as supergrid_cpu evaluates it carries its top piece's closing vertex row; that row belongs to the next slab
+    (to this one only when it is the last): trim x, y, dx, angle_dx to the rows the slab owns, as Supergrid.arrays() does."""
+    n = arrays["area"].shape[0] + (1 if k == V - 1 else 0)
+    return {f: (a[:n] if f in ("x", "y", "dx", "angle_dx") else a) for f, a in arrays.items()}
+
+
+def cpu_slab_checksums(r, r_dp, k, V):
+    """Checker, not a measurement: the CPU oracle's evaluation of row-slab k of V of the timed grid, as six checksums."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import supergrid_cpu
+    out = own_rows(supergrid_cpu.build_cpu(r, r_dp=r_dp, slab=(k, V) if V > 1 else None), k, V)
+    return host_checksums(out), list(out["x"].shape)
 
 
 def cpu_baseline(r, r_dp):
@@ -243,7 +280,10 @@ def run_reference(args):
             "cpu_baseline": {"value": pps, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": sample + "; oracle/ C restatement of the reference with OpenMP on all host threads (the "
                                        "reference itself is pure Python + the absent numpypi and cannot travel to this box)"},
-            "e2e": {"value": pps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+            "e2e": {"value": pps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            # what this arm evaluated in its last timed step, as the same six checksums the GPU arm prints for rank 0's slab
+            "rank0_slab_checksums_x_y_dx_dy_area_angle": host_checksums(own_rows(_LAST_CPU_PASS[0], 0, world)),
+            "rank0_slab": {"slab": [0, world], "shape": list(shape)}}
     print(json.dumps(line))
 
 
@@ -523,6 +563,14 @@ def run_ours(args):
                "checksum_area_local": checksum, "host_area_last_cell": corner, "pinned_on_gpu_numa_node": numa_bound}
         del pinned
 
+    # rank 0's first row-slab of the timed grid as the device holds it after one more build: six checksums, compared with
+    # the CPU oracle's evaluation of the same slab when the line is assembled (outside every timed region)
+    ours_chk = ours_shape = None
+    if rank == 0:
+        sg.set_slab(mine[0], V).build()
+        ours_chk, ours_shape = _u64(sg.checksums()), [sg.vertex_rows, plan.nxp]
+        torch.cuda.synchronize()
+
     # ---- N > 1: the halo path on the wire; every N: the fixed-size (strong-scaling) runs of configs[2..4] -------------
     halo = halo_midas_check(plan, rank, world, dist) if dist is not None else None
     strong = None
@@ -642,6 +690,18 @@ def run_ours(args):
         line["cpu_baseline"] = cpu_baseline(r, args.r_dp)
     elif world > 1:
         line["cpu_baseline"] = None
+    # Parity of the grid that was timed, visible in the line itself: rank 0's first row-slab as the device holds it after
+    # one more build, against the CPU oracle's evaluation of the same slab (outside the timed region; the oracle is the
+    # checker here, never the thing measured).  Six splitmix64 checksums, x y dx dy area angle_dx.
+    line["rank0_slab_checksums_x_y_dx_dy_area_angle"] = line["parity_rank0_slab_equals_cpu"] = None
+    if rank == 0:
+        line["rank0_slab_checksums_x_y_dx_dy_area_angle"] = ours_chk
+        line["rank0_slab"] = {"slab": [mine[0], V], "shape": ours_shape}
+        if not args.no_cpu_baseline:
+            use_all_host_threads()
+            theirs, shape = cpu_slab_checksums(r, args.r_dp, mine[0], V)
+            line["parity_rank0_slab_equals_cpu"] = bool(ours_chk == theirs)
+            line["rank0_slab"]["cpu_shape"] = shape
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
