@@ -283,7 +283,8 @@ def run_reference(args):
             "e2e": {"value": pps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
             # what this arm evaluated in its last timed step, as the same six checksums the GPU arm prints for rank 0's slab
             "rank0_slab_checksums_x_y_dx_dy_area_angle": host_checksums(own_rows(_LAST_CPU_PASS[0], 0, world)),
-            "rank0_slab": {"slab": [0, world], "shape": list(shape)}}
+            "rank0_slab": {"slab": [0, world], "shape": list(own_rows(_LAST_CPU_PASS[0], 0, world)["x"].shape),
+                           "evaluated_shape": list(shape)}}
     print(json.dumps(line))
 
 
